@@ -1,0 +1,151 @@
+/* pie_b200.h -- C ABI of libpie_b200.so: the B200 (sm_100a) implementation of the quantized Llama
+ * decode path of TheProxyCompany/proxy-inference-engine (PIE).
+ *
+ * Every entry point replaces one operator the reference reaches through MLX; the citation beside each
+ * declaration is the reference interface it stands in for.  Shorthands: PIE = src/proxy_inference_engine,
+ * MLX = src/pie_core/external/mlx (both relative to the reference root).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - activations, scales, biases and norm weights are bf16 (uint16 bit patterns); packed weights are
+ *     uint32 in MLX's affine layout: element k of a row lives in bits [bits*(k % (32/bits)), +bits) of
+ *     word k / (32/bits), LSB first (MLX/mlx/backend/cpu/quantized.cpp:648); one (scale, bias) pair per
+ *     `group_size` consecutive elements of a row;
+ *   - all calls are asynchronous on `stream` (a cudaStream_t passed as void*), allocate nothing, keep no
+ *     state, never synchronise: they can be captured in CUDA graphs.  Workspaces are caller-owned;
+ *   - the return value is a pie_status; PIE_ECUDA means a CUDA runtime error (pie_last_cuda_error()).
+ *   - supported set: bits in {4, 8}, group_size 64.  Anything else -> PIE_EUNSUPPORTED (the Python
+ *     wrapper raises ValueError before the call, like MLX/mlx/ops.cpp:82-134 and fast.cpp:839-866).
+ */
+#ifndef PIE_B200_H_
+#define PIE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pie_status {
+  PIE_OK = 0,
+  PIE_EINVAL_SHAPE = 1,  /* a dimension breaks the operator's contract                    */
+  PIE_EINVAL_DTYPE = 2,  /* dtype code not understood                                     */
+  PIE_EUNSUPPORTED = 3,  /* valid for MLX, not built here (bits/group_size/head_dim ...)  */
+  PIE_ECUDA = 4,         /* CUDA error; see pie_last_cuda_error()                          */
+  PIE_ENULL = 5,         /* a required pointer is NULL                                    */
+  PIE_EALIGN = 6         /* a pointer is not 16-byte aligned                               */
+} pie_status;
+
+enum { PIE_DTYPE_BF16 = 0, PIE_DTYPE_F32 = 1 };
+
+/* x-operand preparation of pie_qmv_fused */
+enum { PIE_X_PLAIN = 0, PIE_X_RMSNORM = 1 };
+/* epilogues of pie_qmv_fused */
+enum {
+  PIE_EPI_STORE = 0,   /* out[m, off + n] = bf16(y)                                               */
+  PIE_EPI_RESADD = 1,  /* out[m, n] = bf16(residual[m, n] + bf16(y))     (language.py:150-154)    */
+  PIE_EPI_SILUMUL = 2  /* out[m, n] = silu(bf16(y_gate)) * bf16(y_up)    (language.py:126-127)    */
+};
+
+int pie_abi_version(void);
+const char* pie_status_string(int status);
+const char* pie_last_cuda_error(void);
+/* number of kernels this library has launched since load (the bench's gpu_launches claim) */
+unsigned long long pie_launch_count(void);
+
+/* ---- a1  mx.quantize  (MLX/mlx/ops.cpp:4023-4029 -> MLX/mlx/backend/cpu/quantized.cpp:603-661) -------
+ * w [rows, K] (dtype) -> wq [rows, K*bits/32] u32, scales/biases [rows, K/group_size] (dtype). Bit-exact. */
+int pie_quantize(const void* w, int dtype, uint32_t* wq, void* scales, void* biases, long long rows, int K,
+                 int group_size, int bits, void* stream);
+
+/* ---- a4  mx.dequantize, with the row gather of QuantizedEmbedding.__call__ ---------------------------
+ * (MLX/python/mlx/nn/layers/quantized.py:100-107; MLX/mlx/fast.cpp:972-1017)
+ * out[i, :] = bf16(bf16(q[r] * scales[r]) + biases[r]),  r = ids ? ids[i] : i.   out bf16 [n_rows, K].  */
+int pie_dequantize(void* out, const uint32_t* wq, const void* scales, const void* biases, const int32_t* ids,
+                   long long n_rows, long long table_rows, int K, int group_size, int bits, void* stream);
+
+/* ---- a2/a5  mx.quantized_matmul(x, w, scales, biases, transpose=True) for decode-sized M -------------
+ * (MLX/mlx/ops.cpp:3984-4021; QuantizedLinear.__call__ MLX/python/mlx/nn/layers/quantized.py:204-216;
+ *  replaces Metal qmv_fast, MLX/mlx/backend/metal/kernels/quantized.h:623-689)
+ * y[m, n] = bf16( sum_k x[m, k] * (scales[n, k/gs] * q[n, k] + biases[n, k/gs]) ), fp32 accumulate.
+ * x bf16 [M, K], y bf16 [M, N], 1 <= M <= 8 per launch (larger M: the wrapper loops, or pie_qmm).      */
+int pie_qmv(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
+            int K, int group_size, int bits, void* stream);
+
+/* Fused form used by the decode step: up to 3 weight matrices sharing x (q/k/v), optional RMSNorm on
+ * the way in (a6) and residual-add / SwiGLU on the way out (a11).  For PIE_EPI_SILUMUL pass exactly two
+ * segments (gate, up) of equal N.  residual may alias out.                                             */
+typedef struct pie_qmv_seg {
+  const uint32_t* wq;
+  const void* scales;
+  const void* biases;
+  int N;
+} pie_qmv_seg;
+int pie_qmv_fused(void* out, int out_ld, const void* x, int M, int K, const pie_qmv_seg* segs_host, int nseg,
+                  int group_size, int bits, int xmode, const void* norm_weight, float eps, int epilogue,
+                  const void* residual, int ksplit_hint, void* stream);
+
+/* ---- a3  mx.quantized_matmul for prefill-sized M (replaces Metal qmm_t, kernels/quantized.h:954-1078) -
+ * Same contraction; weights are dequantised to bf16 once per tile (the rounding structure of qmm_t's
+ * QuantizedBlockLoader, kernels/quantized.h:411-417,502-512) and contracted on tcgen05 with fp32
+ * accumulation in TMEM.  x bf16 [M, K] row-major, y bf16 [M, N].                                        */
+int pie_qmm(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
+            int K, int group_size, int bits, void* stream);
+
+/* ---- a6  mx.fast.rms_norm (MLX/mlx/fast.cpp:56-123; kernels/rms_norm.metal:13-81) -------------------- */
+int pie_rms_norm(void* out, const void* x, const void* weight, long long rows, int dims, float eps,
+                 void* stream);
+
+/* ---- a7  mx.fast.rope (MLX/mlx/fast.cpp:353-511) as called by Llama3RoPE (PIE/models/llama/utils.py:42-50)
+ * x, out bf16 [n_batch, L, row_stride >= dims] (n_batch = B*H for [B,H,L,D]); rotates the first `dims`
+ * features; freqs f32 [dims/2] (wavelength-like: theta = pos/freqs[i]) or NULL -> base.                 */
+int pie_rope(void* out, const void* x, long long n_batch, int L, int D, int dims, int traditional, float base,
+             float scale, int offset, const float* freqs, void* stream);
+
+/* ---- a7+a8 fused for decode (L == 1): rotate q and k at position pos[b], append k,v to the cache --------
+ * (Attention.__call__ PIE/models/llama/language.py:84-98; ReusableKVCache.update_and_fetch reusable.py:96-142)
+ * qkv bf16 [B, (Hq + 2 Hkv) * D] as produced by the fused q/k/v projection; q_out bf16 [B, Hq, D].
+ * KV geometry in elements: addr(b, h, t) = base + b*batch_stride + h*head_stride + t*tok_stride, or with
+ * page_table (int32 [B, pt_stride], page_size tokens per page):
+ *   addr = (page_table[b, t / page_size] * page_size + t % page_size) * tok_stride + h * head_stride.   */
+typedef struct pie_kv_layout {
+  long long batch_stride, head_stride, tok_stride;
+  const int32_t* page_table;
+  int pt_stride, page_size;
+} pie_kv_layout;
+int pie_rope_kv_append(void* q_out, const void* qkv, void* kcache, void* vcache, const pie_kv_layout* kv_host,
+                       const int32_t* positions, const float* freqs, int B, int Hq, int Hkv, int D,
+                       void* stream);
+
+/* ---- a8  cache.update_and_fetch for L >= 1 (prefill): copy k,v [B, Hkv, L, D] into the cache at offset - */
+int pie_kv_write(void* kcache, void* vcache, const pie_kv_layout* kv_host, const void* k, const void* v, int B,
+                 int Hkv, int L, int D, int offset, void* stream);
+
+/* ---- a9  mx.fast.scaled_dot_product_attention, L == 1, mask None (PIE/models/base.py:92-113) ----------
+ * split-K flash-decode (the scheme of Metal sdpa_vector_2pass, kernels/sdpa_vector.h:168-392).
+ * q bf16 [B, Hq, D]; context length of row b = positions[b] + 1; out bf16 [B, Hq * D].
+ * workspace: f32, pie_decode_attn_workspace_bytes(B, Hq, D, nsplit) bytes.  nsplit <= 0: library picks. */
+size_t pie_decode_attn_workspace_bytes(int B, int Hq, int D, int nsplit);
+int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context);
+int pie_decode_attn(void* out, const void* q, const void* kcache, const void* vcache,
+                    const pie_kv_layout* kv_host, const int32_t* positions, int B, int Hq, int Hkv, int D,
+                    float scale, int nsplit, void* workspace, void* stream);
+
+/* ---- a10 SDPA for L > 1 with the additive causal mask of create_attention_mask (PIE/models/base.py:18-53)
+ * q bf16 [B, Hq, L, D]; k,v read from the cache (T = offset + L tokens); out bf16 [B, L, Hq * D].       */
+int pie_prefill_attn(void* out, const void* q, const void* kcache, const void* vcache,
+                     const pie_kv_layout* kv_host, int B, int Hq, int Hkv, int L, int D, int offset, float scale,
+                     void* stream);
+
+/* ---- a11 glue: nn.silu(g) * u and h + r, bf16 with a rounding at each MLX op boundary ------------------ */
+int pie_silu_mul(void* out, const void* gate, const void* up, long long n, void* stream);
+int pie_add(void* out, const void* a, const void* b, long long n, void* stream);
+
+/* ---- greedy sampler (temp == 0): arg-max over the vocabulary (PIE/samplers/__init__.py make_sampler) --- */
+int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIE_B200_H_ */
