@@ -34,13 +34,12 @@ typedef enum pie_status {
   PIE_EUNSUPPORTED = 3,  /* valid for MLX, not built here (bits/group_size/head_dim ...)  */
   PIE_ECUDA = 4,         /* CUDA error; see pie_last_cuda_error()                          */
   PIE_ENULL = 5,         /* a required pointer is NULL                                    */
-  PIE_EALIGN = 6         /* a pointer is not 16-byte aligned                               */
+  PIE_EALIGN = 6,        /* a pointer is not 16-byte aligned                               */
+  PIE_EWORKSPACE = 7     /* caller-owned workspace missing or smaller than *_workspace_bytes() */
 } pie_status;
 
 enum { PIE_DTYPE_BF16 = 0, PIE_DTYPE_F32 = 1 };
 
-/* x-operand preparation of pie_qmv_fused */
-enum { PIE_X_PLAIN = 0, PIE_X_RMSNORM = 1 };
 /* epilogues of pie_qmv_fused */
 enum {
   PIE_EPI_STORE = 0,   /* out[m, off + n] = bf16(y)                                               */
@@ -69,29 +68,35 @@ int pie_dequantize(void* out, const uint32_t* wq, const void* scales, const void
  * (MLX/mlx/ops.cpp:3984-4021; QuantizedLinear.__call__ MLX/python/mlx/nn/layers/quantized.py:204-216;
  *  replaces Metal qmv_fast, MLX/mlx/backend/metal/kernels/quantized.h:623-689)
  * y[m, n] = bf16( sum_k x[m, k] * (scales[n, k/gs] * q[n, k] + biases[n, k/gs]) ), fp32 accumulate.
- * x bf16 [M, K], y bf16 [M, N], 1 <= M <= 8 per launch (larger M: the wrapper loops, or pie_qmm).      */
+ * x bf16 [M, K], y bf16 [M, N].  M > 8 runs as passes of 8 rows.
+ * Split-K workspace: pie_qmv_workspace_bytes() bytes, caller-owned, ZEROED ONCE at allocation (the
+ * kernel leaves its counters at zero), never shared by two streams at a time.  `dual` = 1 for the SwiGLU
+ * form of pie_qmv_fused (n_total = N of one of the two matrices), else n_total = sum of the segments' N. */
+size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int dual, int ksplit_hint);
 int pie_qmv(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
-            int K, int group_size, int bits, void* stream);
+            int K, int group_size, int bits, void* workspace, size_t workspace_bytes, void* stream);
 
-/* Fused form used by the decode step: up to 3 weight matrices sharing x (q/k/v), optional RMSNorm on
- * the way in (a6) and residual-add / SwiGLU on the way out (a11).  For PIE_EPI_SILUMUL pass exactly two
- * segments (gate, up) of equal N.  residual may alias out.                                             */
+/* Fused form used by the decode step: up to 3 weight matrices sharing x (q/k/v), optional RMSNorm of x on
+ * the way in (a6: norm_weight != NULL -> x <- rms_norm(x, norm_weight, eps)) and residual-add / SwiGLU on
+ * the way out (a11).  For PIE_EPI_SILUMUL pass exactly two segments (gate, up) of equal N; the output row
+ * is then N wide.  residual (ld = out_ld) may alias out.  x_ld = elements between rows of x.
+ * pdl != 0 launches with programmatic stream serialization: the kernel prefetches its weights while the
+ * previous kernel on the stream drains, and reads x only after that kernel has completed.               */
 typedef struct pie_qmv_seg {
   const uint32_t* wq;
   const void* scales;
   const void* biases;
   int N;
 } pie_qmv_seg;
-int pie_qmv_fused(void* out, int out_ld, const void* x, int M, int K, const pie_qmv_seg* segs_host, int nseg,
-                  int group_size, int bits, int xmode, const void* norm_weight, float eps, int epilogue,
-                  const void* residual, int ksplit_hint, void* stream);
+int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs_host,
+                  int nseg, int group_size, int bits, const void* norm_weight, float eps, int epilogue,
+                  const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl,
+                  void* stream);
 
 /* ---- a3  mx.quantized_matmul for prefill-sized M (replaces Metal qmm_t, kernels/quantized.h:954-1078) -
- * Same contraction; weights are dequantised to bf16 once per tile (the rounding structure of qmm_t's
- * QuantizedBlockLoader, kernels/quantized.h:411-417,502-512) and contracted on tcgen05 with fp32
- * accumulation in TMEM.  x bf16 [M, K] row-major, y bf16 [M, N].                                        */
+ * Same contraction and workspace contract as pie_qmv.  x bf16 [M, K] row-major, y bf16 [M, N].           */
 int pie_qmm(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
-            int K, int group_size, int bits, void* stream);
+            int K, int group_size, int bits, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- a6  mx.fast.rms_norm (MLX/mlx/fast.cpp:56-123; kernels/rms_norm.metal:13-81) -------------------- */
 int pie_rms_norm(void* out, const void* x, const void* weight, long long rows, int dims, float eps,
@@ -125,12 +130,14 @@ int pie_kv_write(void* kcache, void* vcache, const pie_kv_layout* kv_host, const
 /* ---- a9  mx.fast.scaled_dot_product_attention, L == 1, mask None (PIE/models/base.py:92-113) ----------
  * split-K flash-decode (the scheme of Metal sdpa_vector_2pass, kernels/sdpa_vector.h:168-392).
  * q bf16 [B, Hq, D]; context length of row b = positions[b] + 1; out bf16 [B, Hq * D].
- * workspace: f32, pie_decode_attn_workspace_bytes(B, Hq, D, nsplit) bytes.  nsplit <= 0: library picks. */
+ * workspace (nsplit > 1): pie_decode_attn_workspace_bytes(B, Hq, D, nsplit) bytes, caller-owned,
+ * ZEROED ONCE at allocation (counters are left at zero).  nsplit is fixed per launch so the call can be
+ * captured in a CUDA graph; splits beyond the current context are empty and cost nothing.              */
 size_t pie_decode_attn_workspace_bytes(int B, int Hq, int D, int nsplit);
 int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context);
 int pie_decode_attn(void* out, const void* q, const void* kcache, const void* vcache,
                     const pie_kv_layout* kv_host, const int32_t* positions, int B, int Hq, int Hkv, int D,
-                    float scale, int nsplit, void* workspace, void* stream);
+                    float scale, int nsplit, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- a10 SDPA for L > 1 with the additive causal mask of create_attention_mask (PIE/models/base.py:18-53)
  * q bf16 [B, Hq, L, D]; k,v read from the cache (T = offset + L tokens); out bf16 [B, L, Hq * D].       */
@@ -142,8 +149,12 @@ int pie_prefill_attn(void* out, const void* q, const void* kcache, const void* v
 int pie_silu_mul(void* out, const void* gate, const void* up, long long n, void* stream);
 int pie_add(void* out, const void* a, const void* b, long long n, void* stream);
 
-/* ---- greedy sampler (temp == 0): arg-max over the vocabulary (PIE/samplers/__init__.py make_sampler) --- */
-int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, void* stream);
+/* ---- greedy sampler (temp == 0): first arg-max over the vocabulary (PIE/samplers/__init__.py make_sampler).
+ * positions_to_advance (optional, int32 [rows]) is incremented by one per row: the device-side
+ * `cache.offset += 1` of the decode loop (PIE/engine/inference_engine.py:282-297), so that a captured
+ * step can be replayed without host involvement.                                                        */
+int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_t* positions_to_advance,
+               void* stream);
 
 #ifdef __cplusplus
 }

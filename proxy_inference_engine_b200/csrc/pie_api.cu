@@ -1,0 +1,179 @@
+// C ABI of libpie_b200.so (include/pie_b200.h): argument validation + dispatch.  No allocation, no state
+// beyond a launch counter and the last CUDA error string.
+#include "../../include/pie_b200.h"
+#include "pie_internal.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+namespace pie {
+static std::atomic<unsigned long long> g_launches{0};
+static thread_local char g_cuda_err[256] = "";
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+static int cuda_status(cudaError_t e) {
+  if (e == cudaSuccess) return PIE_OK;
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", cudaGetErrorName(e), cudaGetErrorString(e));
+  return PIE_ECUDA;
+}
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static inline bool quant_supported(int gs, int bits) { return gs == 64 && (bits == 4 || bits == 8); }
+static inline int stage_k(int bits) { return kRowBytes * 8 / bits; }
+
+struct QmvPlan { int warps, ksplit, kslice, ntiles; };
+
+static QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint) {
+  QmvPlan p;
+  p.warps = 4;
+  if (const char* e = getenv("PIE_QMV_WARPS")) { int w = atoi(e); if (w == 4 || w == 8) p.warps = w; }
+  p.ntiles = (int)((rows_total + (dual ? 7 : 15)) / (dual ? 8 : 16));
+  const int ck = stage_k(bits), chunks = K / ck;
+  int target = 148 * 4;
+  if (const char* e = getenv("PIE_QMV_TARGET_CTAS")) { int t = atoi(e); if (t > 0) target = t; }
+  int ks = ksplit_hint > 0 ? ksplit_hint : (target + p.ntiles - 1) / p.ntiles;
+  int max_ks = chunks / p.warps; if (max_ks < 1) max_ks = 1;
+  if (ks > max_ks) ks = max_ks;
+  if (ks < 1) ks = 1;
+  // shared-memory bound on the x slice: M * kslice * 2 bytes <= 96 KB
+  const int max_slice = (96 * 1024 / (2 * (M > 0 ? M : 1))) / ck * ck;
+  int per = (chunks + ks - 1) / ks;
+  if (per * ck > max_slice) per = max_slice / ck;
+  if (per < 1) per = 1;
+  p.kslice = per * ck;
+  p.ksplit = (K + p.kslice - 1) / p.kslice;
+  return p;
+}
+static size_t qmv_ws_bytes(const QmvPlan& p) {
+  if (p.ksplit <= 1) return 0;
+  const size_t cnt = (((size_t)p.ntiles * 4) + 255) & ~(size_t)255;
+  return cnt + (size_t)p.ntiles * p.ksplit * 128 * sizeof(float);
+}
+}  // namespace pie
+
+using namespace pie;
+
+extern "C" {
+
+int pie_abi_version(void) { return 2; }
+const char* pie_status_string(int s) {
+  switch (s) {
+    case PIE_OK: return "ok";
+    case PIE_EINVAL_SHAPE: return "invalid shape";
+    case PIE_EINVAL_DTYPE: return "invalid dtype";
+    case PIE_EUNSUPPORTED: return "unsupported configuration";
+    case PIE_ECUDA: return "CUDA error";
+    case PIE_ENULL: return "null pointer";
+    case PIE_EALIGN: return "pointer not 16-byte aligned";
+    case PIE_EWORKSPACE: return "workspace too small";
+    default: return "unknown";
+  }
+}
+const char* pie_last_cuda_error(void) { return g_cuda_err; }
+unsigned long long pie_launch_count(void) { return g_launches.load(); }
+
+int pie_quantize(const void* w, int dtype, uint32_t* wq, void* scales, void* biases, long long rows, int K,
+                 int group_size, int bits, void* stream) {
+  if (!w || !wq || !scales || !biases) return rows == 0 ? PIE_OK : PIE_ENULL;
+  if (dtype != PIE_DTYPE_BF16 && dtype != PIE_DTYPE_F32) return PIE_EINVAL_DTYPE;
+  if (group_size != 32 && group_size != 64 && group_size != 128) return PIE_EUNSUPPORTED;
+  if (bits != 2 && bits != 4 && bits != 8) return PIE_EUNSUPPORTED;
+  if (rows < 0 || K <= 0 || K % group_size != 0) return PIE_EINVAL_SHAPE;
+  return cuda_status(launch_quantize(w, dtype, wq, scales, biases, rows, K, group_size, bits, (cudaStream_t)stream));
+}
+
+int pie_dequantize(void* out, const uint32_t* wq, const void* scales, const void* biases, const int32_t* ids,
+                   long long n_rows, long long table_rows, int K, int group_size, int bits, void* stream) {
+  if (n_rows == 0) return PIE_OK;
+  if (!out || !wq || !scales || !biases) return PIE_ENULL;
+  if (group_size != 32 && group_size != 64 && group_size != 128) return PIE_EUNSUPPORTED;
+  if (bits != 2 && bits != 4 && bits != 8) return PIE_EUNSUPPORTED;
+  if (n_rows < 0 || table_rows <= 0 || K <= 0 || K % group_size != 0) return PIE_EINVAL_SHAPE;
+  return cuda_status(launch_dequantize((uint16_t*)out, wq, (const uint16_t*)scales, (const uint16_t*)biases, ids,
+                                       n_rows, table_rows, K, group_size, bits, nullptr, (cudaStream_t)stream));
+}
+
+size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int dual, int ksplit_hint) {
+  if (M <= 0 || n_total <= 0 || K <= 0 || (bits != 4 && bits != 8) || K % stage_k(bits) != 0) return 0;
+  QmvPlan p = plan_qmv(M > kMaxBatch ? kMaxBatch : M, n_total, K, bits, dual, ksplit_hint);
+  p.ntiles += kMaxSeg;  // segments are tiled separately: up to one ragged tile each
+  return qmv_ws_bytes(p);
+}
+
+int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
+                  int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
+                  int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
+  if (M == 0) return PIE_OK;
+  if (!out || !x || !segs) return PIE_ENULL;
+  if (!quant_supported(group_size, bits)) return PIE_EUNSUPPORTED;
+  if (nseg < 1 || nseg > kMaxSeg || M < 0 || K <= 0 || K % group_size != 0) return PIE_EINVAL_SHAPE;
+  if (K % stage_k(bits) != 0 || x_ld % 8 != 0 || x_ld < K) return PIE_EUNSUPPORTED;
+  if (epilogue < PIE_EPI_STORE || epilogue > PIE_EPI_SILUMUL) return PIE_EINVAL_SHAPE;
+  if (epilogue == PIE_EPI_RESADD && !residual) return PIE_ENULL;
+  const int dual = epilogue == PIE_EPI_SILUMUL;
+  if (dual && (nseg != 2 || segs[0].N != segs[1].N)) return PIE_EINVAL_SHAPE;
+  if (!aligned16(x) || (norm_weight && !aligned16(norm_weight))) return PIE_EALIGN;
+  QmvArgs a;
+  memset(&a, 0, sizeof(a));
+  long long rows_total = 0;
+  int tile = 0, off = 0;
+  for (int i = 0; i < nseg; ++i) {
+    if (!segs[i].wq || !segs[i].scales || !segs[i].biases) return PIE_ENULL;
+    if (segs[i].N <= 0) return PIE_EINVAL_SHAPE;
+    if (!aligned16(segs[i].wq) || (reinterpret_cast<uintptr_t>(segs[i].scales) & 7) ||
+        (reinterpret_cast<uintptr_t>(segs[i].biases) & 7)) return PIE_EALIGN;
+    a.seg[i].wq = segs[i].wq;
+    a.seg[i].scales = (const uint16_t*)segs[i].scales;
+    a.seg[i].biases = (const uint16_t*)segs[i].biases;
+    a.seg[i].N = segs[i].N;
+    a.seg[i].tile0 = tile;
+    a.seg[i].out_off = off;
+    tile += (segs[i].N + 15) / 16;
+    off += segs[i].N;
+    rows_total += segs[i].N;
+  }
+  if (dual) rows_total = segs[0].N;
+  if (out_ld < (dual ? segs[0].N : off)) return PIE_EINVAL_SHAPE;
+  a.nseg = nseg; a.dual = dual; a.K = K; a.x_ld = x_ld;
+  a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
+  a.out_ld = out_ld; a.epi = epilogue;
+  for (int m0 = 0; m0 < M; m0 += kMaxBatch) {
+    const int mb = M - m0 < kMaxBatch ? M - m0 : kMaxBatch;
+    QmvPlan p = plan_qmv(mb, rows_total, K, bits, dual, ksplit_hint);
+    if (!dual) p.ntiles = tile;
+    const size_t need = qmv_ws_bytes(p);
+    if (need > workspace_bytes || (need && !workspace)) return PIE_EWORKSPACE;
+    a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice;
+    a.x = (const uint16_t*)x + (size_t)m0 * x_ld;
+    a.out = (uint16_t*)out + (size_t)m0 * out_ld;
+    a.residual = residual ? (const uint16_t*)residual + (size_t)m0 * out_ld : nullptr;
+    a.ws_cnt = (unsigned int*)workspace;
+    a.ws_part = (float*)((uint8_t*)workspace + ((((size_t)p.ntiles * 4) + 255) & ~(size_t)255));
+    const int st = cuda_status(launch_qmv(a, bits, p.warps, pdl != 0, (cudaStream_t)stream));
+    if (st != PIE_OK) return st;
+  }
+  return PIE_OK;
+}
+
+int pie_qmv(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
+            int K, int group_size, int bits, void* workspace, size_t workspace_bytes, void* stream) {
+  if (M == 0 || N == 0) return PIE_OK;
+  if (!y || !x || !wq || !scales || !biases) return PIE_ENULL;
+  if (M < 0 || N < 0 || K <= 0) return PIE_EINVAL_SHAPE;
+  const bool fast = quant_supported(group_size, bits) && K % stage_k(bits) == 0 && aligned16(x) && aligned16(wq) &&
+                    !(reinterpret_cast<uintptr_t>(scales) & 7) && !(reinterpret_cast<uintptr_t>(biases) & 7);
+  if (fast) {
+    pie_qmv_seg seg = {wq, scales, biases, N};
+    return pie_qmv_fused(y, N, x, K, M, K, &seg, 1, group_size, bits, nullptr, 0.f, PIE_EPI_STORE, nullptr, 0,
+                         workspace, workspace_bytes, 0, stream);
+  }
+  if (group_size != 32 && group_size != 64 && group_size != 128) return PIE_EUNSUPPORTED;
+  if (bits != 2 && bits != 4 && bits != 8) return PIE_EUNSUPPORTED;
+  if (K % group_size != 0) return PIE_EINVAL_SHAPE;
+  return cuda_status(launch_qmv_generic((uint16_t*)y, (const uint16_t*)x, wq, (const uint16_t*)scales,
+                                        (const uint16_t*)biases, M, N, K, group_size, bits, (cudaStream_t)stream));
+}
+
+}  // extern "C"
+#include "pie_api2.inl"

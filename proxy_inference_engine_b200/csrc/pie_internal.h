@@ -1,0 +1,88 @@
+// Private launch descriptors shared by the C-ABI layer (pie_api.cu) and the kernels.
+// Nothing here is part of the public ABI (include/pie_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pie {
+
+constexpr int kGroup = 64;      // the only group size on the fast path
+constexpr int kTileRows = 16;   // one mma.sync m16 tile of weight rows
+constexpr int kMaxBatch = 8;    // mma.sync n8: activation rows per qmv pass
+constexpr int kMaxSeg = 3;      // q / k / v   or   gate / up
+constexpr int kRowBytes = 128;  // bytes of one weight row per ring stage (256 q4 / 128 q8 elements)
+constexpr int kQmvStages = 4;   // per-warp cp.async ring depth
+
+enum Epilogue : int { EPI_STORE = 0, EPI_RESADD = 1, EPI_SILUMUL = 2 };
+
+struct QmvSeg {
+  const uint32_t* wq;
+  const uint16_t* scales;
+  const uint16_t* biases;
+  int N;        // rows of this matrix
+  int tile0;    // first tile index of this segment
+  int out_off;  // column offset of this segment in the output row
+};
+
+struct QmvArgs {
+  QmvSeg seg[kMaxSeg];
+  int nseg;
+  int dual;      // 1: seg[0] = gate, seg[1] = up; a tile is 8 gate rows + 8 up rows (SwiGLU epilogue)
+  int M, K;
+  int ntiles;
+  int ksplit;    // gridDim.y
+  int kslice;    // elements of K per split (multiple of the stage's K extent)
+  const uint16_t* x;  // bf16 [M, K]
+  int x_ld;
+  // optional fused RMSNorm of x: x <- bf16(bf16(x * inv_rms) * norm_w)   (inv_rms computed per CTA over full K)
+  const uint16_t* norm_w;
+  float eps;
+  uint16_t* out;
+  int out_ld;
+  const uint16_t* residual;  // EPI_RESADD (ld = out_ld)
+  int epi;
+  float* ws_part;        // [ntiles][ksplit][128] fp32, only if ksplit > 1
+  unsigned int* ws_cnt;  // [ntiles], zero before the first launch, self-cleaning
+};
+
+struct KvLayout {
+  long long batch_stride, head_stride, tok_stride;
+  const int32_t* page_table;
+  int pt_stride, page_size;
+};
+
+// ---- launchers (return cudaError_t of the launch) -------------------------------------------------
+cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStream_t st);
+cudaError_t launch_qmv_generic(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s,
+                               const uint16_t* b, int M, int N, int K, int gs, int bits, cudaStream_t st);
+size_t qmv_smem_bytes(int M, int kslice, int bits, int warps);
+
+cudaError_t launch_quantize(const void* w, int dtype, uint32_t* wq, void* s, void* b, long long rows, int K,
+                            int gs, int bits, cudaStream_t st);
+cudaError_t launch_dequantize(uint16_t* out, const uint32_t* wq, const uint16_t* s, const uint16_t* b,
+                              const int32_t* ids, long long n_rows, long long table_rows, int K, int gs,
+                              int bits, int* err_flag, cudaStream_t st);
+cudaError_t launch_rms_norm(uint16_t* out, const uint16_t* x, const uint16_t* w, long long rows, int dims,
+                            float eps, cudaStream_t st);
+cudaError_t launch_rope(uint16_t* out, const uint16_t* x, long long n_batch, int L, int D, int dims,
+                        int traditional, float base, float scale, int offset, const float* freqs,
+                        cudaStream_t st);
+cudaError_t launch_rope_kv_append(uint16_t* q_out, const uint16_t* qkv, uint16_t* kc, uint16_t* vc,
+                                  const KvLayout& kv, const int32_t* pos, const float* freqs, int B, int Hq,
+                                  int Hkv, int D, cudaStream_t st);
+cudaError_t launch_kv_write(uint16_t* kc, uint16_t* vc, const KvLayout& kv, const uint16_t* k,
+                            const uint16_t* v, int B, int Hkv, int L, int D, int offset, cudaStream_t st);
+cudaError_t launch_decode_attn(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
+                               const KvLayout& kv, const int32_t* pos, int B, int Hq, int Hkv, int D,
+                               float scale, int nsplit, float* ws, cudaStream_t st);
+cudaError_t launch_prefill_attn(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
+                                const KvLayout& kv, int B, int Hq, int Hkv, int L, int D, int offset,
+                                float scale, cudaStream_t st);
+cudaError_t launch_silu_mul(uint16_t* out, const uint16_t* g, const uint16_t* u, long long n, cudaStream_t st);
+cudaError_t launch_add(uint16_t* out, const uint16_t* a, const uint16_t* b, long long n, cudaStream_t st);
+cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vocab, int32_t* pos_adv,
+                          cudaStream_t st);
+
+void count_launch(int n = 1);
+
+}  // namespace pie

@@ -1,0 +1,63 @@
+// Launcher of the decode GEMV and the slow generic kernel for shapes off the fast path.
+namespace pie {
+
+cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStream_t st) {
+  const size_t smem = qmv_smem_bytes(a.M, a.kslice, bits, warps);
+  auto kern = bits == 4 ? qmv_kernel<4> : qmv_kernel<8>;
+  static size_t configured[2] = {0, 0};  // largest dynamic smem opted in so far, per instantiation
+  size_t& conf = configured[bits == 4 ? 0 : 1];
+  if (smem > conf) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    conf = 227 * 1024;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)a.ntiles, (unsigned)a.ksplit, 1);
+  cfg.blockDim = dim3((unsigned)warps * 32, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, kern, a);
+}
+
+// One warp per output row, any M; bits in {2,4,8}, group_size in {32,64,128}.  fp32, k-ordered per lane.
+__global__ void qmv_generic_kernel(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s,
+                                   const uint16_t* b, int M, int N, int K, int gs, int bits) {
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const int per = 32 / bits;
+  const uint32_t mask = (1u << bits) - 1u;
+  const uint32_t* wr = wq + (size_t)n * (K / per);
+  const int gpr = K / gs;
+  for (int m = 0; m < M; ++m) {
+    float acc = 0.f;
+    for (int wi = lane; wi < K / per; wi += 32) {
+      const uint32_t w = wr[wi];
+      const int kb = wi * per;
+      const int grp = kb / gs;  // a word never straddles a group (gs % per == 0)
+      const float sc = bf16lo((uint32_t)s[(size_t)n * gpr + grp]), bi = bf16lo((uint32_t)b[(size_t)n * gpr + grp]);
+      for (int e = 0; e < per; ++e) {
+        const float q = (float)((w >> (e * bits)) & mask);
+        acc += bf16lo((uint32_t)x[(size_t)m * K + kb + e]) * (sc * q + bi);
+      }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) y[(size_t)m * N + n] = f2bf(acc);
+  }
+}
+
+cudaError_t launch_qmv_generic(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s,
+                               const uint16_t* b, int M, int N, int K, int gs, int bits, cudaStream_t st) {
+  const int wpb = 8;
+  count_launch();
+  qmv_generic_kernel<<<(N + wpb - 1) / wpb, wpb * 32, 0, st>>>(y, x, wq, s, b, M, N, K, gs, bits);
+  return cudaGetLastError();
+}
+
+}  // namespace pie
