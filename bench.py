@@ -1,0 +1,319 @@
+"""bench.py -- decode tok/s of the B200 quantized-Llama path (BASELINE.json configs[1]: Llama-3.1-8B, MLX q4 gs64,
+bs1 decode) with the HBM roofline of its dominant kernel and the reference's CPU path timed beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--model llama-3.1-8b] [--bits 4] [--batch 1]
+
+A step is one decode token for every sequence of the batch (one pass of the hot path).  `value` is device-timed
+(CUDA events around K graph replays, token ids resident on the device); `e2e` drives the same step from HOST
+buffers: token id copied in from pinned memory, sampled token copied back and synchronised, every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--model", default="llama-3.1-8b")
+    ap.add_argument("--bits", type=int, default=4)
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--prompt", type=int, default=128)
+    ap.add_argument("--layers", type=int, default=0, help="debug only: override the layer count (marks the line invalid)")
+    ap.add_argument("--paged", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernel-timing", action="store_true")
+    return ap.parse_args()
+
+
+def model_numbers(args, bits):
+    """Algorithmic bytes per decode step: packed W + bf16 scales + bf16 biases, read once per step."""
+    h, f, L, V = args.hidden_size, args.intermediate_size, args.num_hidden_layers, args.vocab_size
+    nh, nkv = args.num_attention_heads, args.num_key_value_heads
+    d = args.head_dim
+    per_layer = h * (nh * d) + 2 * h * (nkv * d) + (nh * d) * h + 3 * h * f
+    head = V * h
+    params = L * per_layer + head
+    bpp = bits / 8 + 4 / 64
+    kv_per_tok = L * 2 * nkv * d * 2
+    return {"params": params, "weight_bytes": params * bpp, "kv_bytes_per_ctx_token": kv_per_tok,
+            "embed_row_bytes": h * bpp, "bpp": bpp}
+
+
+# ------------------------------------------------------------------------------------------ CPU baseline
+def cpu_baseline(margs, bits, steps=1, warmup=0, budget_s=20.0):
+    """The reference's own `_qmm_t<float, bits, 64>` (MLX/mlx/backend/cpu/quantized.cpp:96-153, compiled where it lies
+    into oracle/_ref) on the decode shapes of this model, M = 1, row-sliced over the host's threads; falls back to
+    the oracle port when oracle/_ref is absent.  Sample: `n_layers_sample` transformer layers' seven matmuls;
+    tok/s extrapolated by parameter count (the path is a pure weight stream)."""
+    import numpy as np
+    from oracle import oracle as orc
+
+    R = orc.ref()
+    kind = "reference" if R is not None else "port"
+    nthreads = (R.pie_ref_max_threads() if R is not None else orc.lib().orc_max_threads())
+    h, f = margs.hidden_size, margs.intermediate_size
+    nh, nkv, d = margs.num_attention_heads, margs.num_key_value_heads, margs.head_dim
+    shapes = [(nh * d, h), (nkv * d, h), (nkv * d, h), (h, nh * d), (f, h), (f, h), (h, f)]
+    rng = np.random.default_rng(0)
+    mats = []
+    for n, k in shapes:
+        wq = rng.integers(0, 2**32, (n, k * bits // 32), dtype=np.uint32)
+        s = (rng.random((n, k // 64), dtype=np.float32) * 0.01).astype(np.float32)
+        b = (rng.random((n, k // 64), dtype=np.float32) * -0.05).astype(np.float32)
+        x = rng.standard_normal((1, k)).astype(np.float32)
+        mats.append((n, k, wq, s, b, x, np.empty((1, n), np.float32)))
+    layer_params = sum(n * k for n, k in shapes)
+
+    def one_layer():
+        for n, k, wq, s, b, x, y in mats:
+            if R is not None:
+                R.pie_ref_qmm_t_f32_mt(y.reshape(-1), x.reshape(-1), wq.reshape(-1), s.reshape(-1), b.reshape(-1),
+                                       1, n, k, bits, 64, nthreads)
+            else:
+                orc.lib().orc_qmm_t(y.reshape(-1), x.reshape(-1), wq.reshape(-1), s.reshape(-1), b.reshape(-1),
+                                    1, n, k, bits, 64, 0)
+
+    t0 = time.perf_counter(); one_layer(); t_probe = time.perf_counter() - t0
+    n_layers_sample = max(1, min(margs.num_hidden_layers, int(budget_s / max(t_probe, 1e-3) / max(steps + warmup, 1))))
+    for _ in range(warmup):
+        for _ in range(n_layers_sample):
+            one_layer()
+    times = []
+    for _ in range(max(steps, 1)):
+        t0 = time.perf_counter()
+        for _ in range(n_layers_sample):
+            one_layer()
+        times.append(time.perf_counter() - t0)
+    t_step = sum(times) / len(times)
+    total_params = model_numbers(margs, bits)["params"]
+    tok_s = 1.0 / (t_step * total_params / (layer_params * n_layers_sample))
+    return {"value": tok_s, "unit": "tok/s", "cores": int(nthreads), "kind": kind,
+            "sample": f"{n_layers_sample} transformer layer(s) x 7 quantized matmuls at M=1 (fp32 _qmm_t, "
+                      f"{layer_params * n_layers_sample / 1e6:.0f} M params of {total_params / 1e6:.0f} M), "
+                      f"extrapolated by parameter count; {t_step:.3f} s per sample",
+            "ms_per_step": t_step * 1e3 * total_params / (layer_params * n_layers_sample)}
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        if sm:
+            sm.sort()
+            out = {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def time_qmv_launches(eng, n_steps=3):
+    """Average device duration of the dominant kernel (qmv_kernel): an eager pass (no graph, no PDL overlap) with a
+    CUDA-event pair around every pie_qmv_fused launch, on the launching stream."""
+    import torch
+    saved = (eng.tokens.clone(), eng.positions.clone(), eng.seq.clone())
+    pairs = []
+    orig = eng._qmv
+    pdl0 = eng.pdl
+    eng.pdl = 0
+
+    def timed(*a, **k):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); orig(*a, **k); e1.record()
+        pairs.append((e0, e1))
+
+    eng._qmv = timed
+    try:
+        for _ in range(n_steps):
+            eng._step_kernels()
+        torch.cuda.synchronize()
+    finally:
+        eng._qmv, eng.pdl = orig, pdl0
+        eng._restore(saved)
+    per_step = len(pairs) // n_steps
+    ms = sum(e0.elapsed_time(e1) for e0, e1 in pairs[per_step:]) / max(n_steps - 1, 1)  # skip the first (cold) step
+    return ms * 1e-3, per_step
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+
+    from proxy_inference_engine_b200 import ops
+    from proxy_inference_engine_b200.checkpoint import build_model, preset_args, random_weights
+    from proxy_inference_engine_b200.decode import DecodeEngine
+
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    over = {"num_hidden_layers": a.layers} if a.layers else {}
+    margs = preset_args(a.model, bits=a.bits, **over)
+    torch.manual_seed(0)
+    weights = random_weights(margs, seed=0, device="cuda")
+    model = build_model(margs, weights)
+    del weights
+    B = a.batch
+    max_ctx = a.prompt + a.warmup + a.steps * 2 + 64
+    eng = DecodeEngine(model, batch=B, max_context=max_ctx, paged=a.paged)
+    prompt = torch.randint(0, margs.vocab_size, (B, a.prompt), generator=torch.Generator().manual_seed(1))
+    eng.prefill(prompt)
+    eng.step(max(a.warmup, 3))
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed region: K graph replays, token ids resident --------------------------------------------------
+    ctx0 = int(eng.positions[0].item())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    e0.record()
+    eng.step(a.steps)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    # ---- end-to-end region: host token in, host token out, every step ------------------------------------------------
+    pin_in = torch.zeros((B,), dtype=torch.int32).pin_memory()
+    pin_out = torch.zeros((B,), dtype=torch.int32).pin_memory()
+    pin_in.copy_(eng.tokens.cpu())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        eng.tokens.copy_(pin_in, non_blocking=True)      # H2D: this step's input token ids
+        eng.step(1)
+        pin_out.copy_(eng.tokens, non_blocking=True)     # D2H: the sampled token ids
+        torch.cuda.current_stream().synchronize()
+        pin_in.copy_(pin_out)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    nums = model_numbers(margs, a.bits)
+    ctx_mid = ctx0 + a.steps / 2
+    step_bytes = nums["weight_bytes"] + B * (ctx_mid * nums["kv_bytes_per_ctx_token"] + nums["embed_row_bytes"])
+    peak, peak_src = measured_peaks()
+    value = world * B * a.steps / (ms * 1e-3)
+    line = {
+        "metric": "decode tok/s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": a.steps,
+        "warmup": max(a.warmup, 3), "ms_per_step": round(ms / a.steps, 5), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16 activations / fp32 accumulate over u4 weights"
+        if a.bits == 4 else "bf16 activations / fp32 accumulate over u8 weights", "data": "synthetic",
+        "config": {"workload": f"{a.model} random-init MLX q{a.bits} gs64, bs{B} greedy decode, prompt {a.prompt}, "
+                               f"context {ctx0}..{ctx0 + a.steps}" + (", paged KV" if a.paged else ""),
+                   "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (TP not built yet)",
+                   "l2": "each step streams the whole weight set (>> 126 MB L2), no flush needed",
+                   "layers": margs.num_hidden_layers},
+        "e2e": {"value": round(world * B * a.steps / (e2e_ms * 1e-3), 2), "unit": "tok/s",
+                "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B},
+        "gpu_launches": eng.launches_per_step * a.steps,
+        "clocks": clocks,
+        "step_roofline": {"bytes_per_step": int(step_bytes), "achieved_GBps": round(step_bytes / (ms / a.steps) / 1e6, 1),
+                          "frac": round(step_bytes / (ms / a.steps) / 1e6 / peak, 4)},
+    }
+    if a.layers:
+        line["invalid"] = "layer count overridden (debug run)"
+    if not a.no_kernel_timing:
+        qsec, nlaunch = time_qmv_launches(eng)
+        qbytes = nums["weight_bytes"]  # every qmv launch of a step together reads the weight set once
+        ach = qbytes / qsec / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}>", "achieved": round(ach, 1), "peak": peak,
+                            "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                            "launches_per_step": nlaunch, "avg_launch_us": round(qsec / nlaunch * 1e6, 2),
+                            "algorithmic_bytes_per_launch": int(qbytes / nlaunch),
+                            "how": "CUDA-event pair around each launch in an eager pass (no graph / PDL)"}
+    if not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(margs, a.bits)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
+    if rank != 0:
+        return
+    from proxy_inference_engine_b200.checkpoint import preset_args
+    margs = preset_args(a.model, bits=a.bits)
+    steps, warm = min(a.steps, 4), min(a.warmup, 1)
+    cb = cpu_baseline(margs, a.bits, steps=steps, warmup=warm, budget_s=60.0)
+    line = {"impl": "reference", "metric": "decode tok/s", "value": round(cb["value"], 4), "unit": "tok/s",
+            "n_gpus": world, "steps": steps, "warmup": warm, "ms_per_step": round(cb["ms_per_step"], 2),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{a.model} random-init MLX q{a.bits} gs64, bs{a.batch} greedy decode "
+                                   "(reference CPU _qmm_t on the host cores; bounded sample)"},
+            "cpu_baseline": cb, "gpu_launches": 0,
+            "e2e": {"value": round(cb["value"], 4), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -152,9 +152,10 @@ int pie_add(void* out, const void* a, const void* b, long long n, void* stream);
 /* ---- greedy sampler (temp == 0): first arg-max over the vocabulary (PIE/samplers/__init__.py make_sampler).
  * positions_to_advance (optional, int32 [rows]) is incremented by one per row: the device-side
  * `cache.offset += 1` of the decode loop (PIE/engine/inference_engine.py:282-297), so that a captured
- * step can be replayed without host involvement.                                                        */
+ * step can be replayed without host involvement.  seq_out (optional, int32 [rows, seq_ld]) is the
+ * device-side token list of the engine: the sampled token is also stored at seq_out[row, new position].  */
 int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_t* positions_to_advance,
-               void* stream);
+               int32_t* seq_out, int seq_ld, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,160 @@
+"""Checkpoint boundary of the path: MLX-layout quantized Llama checkpoints.
+
+``load_model`` mirrors PIE/models/utils.py:51-125: read ``config.json`` + every ``model*.safetensors``, build
+``Model(ModelArgs)``, ``sanitize``, and assign ``weight`` (U32 words) / ``scales`` / ``biases`` (BF16) to the
+quantized layers named by ``config["quantization"]``.  ``random_weights`` is the synthetic-checkpoint generator
+of the benchmarks: nn.Linear / nn.Embedding initialisers, bf16, quantized with the library's
+bit-exact ``quantize``.
+"""
+from __future__ import annotations
+
+import glob
+import json
+import math
+import os
+
+import torch
+
+from . import ops
+from .llama import Model, ModelArgs
+
+LLAMA_PRESETS = {
+    # SURVEY.md section 8 header; defaults of PIE/models/llama/language.py:13-29
+    "llama-3.2-1b": dict(hidden_size=2048, num_hidden_layers=16, intermediate_size=8192, num_attention_heads=32,
+                         num_key_value_heads=8, head_dim=64, vocab_size=128256, tie_word_embeddings=True,
+                         rope_scaling={"factor": 32.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0}),
+    "llama-3.1-8b": dict(hidden_size=4096, num_hidden_layers=32, intermediate_size=14336, num_attention_heads=32,
+                         num_key_value_heads=8, head_dim=128, vocab_size=128256, tie_word_embeddings=False,
+                         rope_scaling={"factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0}),
+    "llama-3.1-70b": dict(hidden_size=8192, num_hidden_layers=80, intermediate_size=28672, num_attention_heads=64,
+                          num_key_value_heads=8, head_dim=128, vocab_size=128256, tie_word_embeddings=False,
+                          rope_scaling={"factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0}),
+}
+
+
+def preset_args(name: str, bits: int = 4, group_size: int = 64, **overrides) -> ModelArgs:
+    cfg = dict(LLAMA_PRESETS[name], rms_norm_eps=1e-5, rope_theta=500000.0, max_position_embeddings=131072,
+               quantization={"group_size": group_size, "bits": bits})
+    cfg.update(overrides)
+    return ModelArgs(**cfg)
+
+
+def _linear_names(args: ModelArgs):
+    h, f = args.hidden_size, args.intermediate_size
+    nh = args.num_attention_heads
+    nkv = args.num_key_value_heads or nh
+    d = args.head_dim or h // nh
+    for i in range(args.num_hidden_layers):
+        p = f"model.layers.{i}"
+        yield p + ".self_attn.q_proj", nh * d, h
+        yield p + ".self_attn.k_proj", nkv * d, h
+        yield p + ".self_attn.v_proj", nkv * d, h
+        yield p + ".self_attn.o_proj", h, nh * d
+        yield p + ".mlp.gate_proj", f, h
+        yield p + ".mlp.down_proj", h, f
+        yield p + ".mlp.up_proj", f, h
+    if not args.tie_word_embeddings:
+        yield "lm_head", args.vocab_size, h
+
+
+def random_weights(args: ModelArgs, seed: int = 0, device="cuda", gen_device=None, head_gain: float = 1.0) -> dict:
+    """Random-init checkpoint in the MLX schema.  Linear: U(-1/sqrt(K), 1/sqrt(K)) (MLX nn/layers/linear.py:51-56);
+    embedding: N(0, 1/sqrt(h)) (embedding.py:25); norm weights 1 + 0.1 N(0,1) so the weight multiply is exercised.
+    ``gen_device='cpu'`` makes the values independent of the GPU (the parity fixtures use it)."""
+    gen_device = gen_device or device
+    g = torch.Generator(device=gen_device).manual_seed(seed)
+    gs, bits = args.quantization["group_size"], args.quantization["bits"]
+    w = {}
+
+    def put_quant(name, t):
+        wq, s, b = ops.quantize(t.to(torch.bfloat16).to(device), gs, bits)
+        w[name + ".weight"], w[name + ".scales"], w[name + ".biases"] = wq, s, b
+
+    h = args.hidden_size
+    emb = torch.randn((args.vocab_size, h), generator=g, device=gen_device) * math.sqrt(1.0 / h)
+    if args.tie_word_embeddings:
+        emb = emb * head_gain
+    put_quant("model.embed_tokens", emb)
+    del emb
+    for name, n, k in _linear_names(args):
+        t = (torch.rand((n, k), generator=g, device=gen_device) * 2 - 1) * math.sqrt(1.0 / k)
+        if name == "lm_head":
+            t = t * head_gain
+        put_quant(name, t)
+        del t
+    for i in range(args.num_hidden_layers):
+        for nm in ("input_layernorm", "post_attention_layernorm"):
+            w[f"model.layers.{i}.{nm}.weight"] = (1 + 0.1 * torch.randn((h,), generator=g, device=gen_device)).to(
+                torch.bfloat16).to(device)
+    w["model.norm.weight"] = (1 + 0.1 * torch.randn((h,), generator=g, device=gen_device)).to(torch.bfloat16).to(device)
+    return w
+
+
+def build_model(args: ModelArgs, weights: dict, device="cuda") -> Model:
+    """Model shell + load_weights, skipping the random initialisers of the layer constructors."""
+    model = _empty_model(args, device)
+    weights = model.sanitize(dict(weights))
+    model.load_weights({k: _as_param(v, device) for k, v in weights.items()}, strict=True)
+    return model
+
+
+def _as_param(v: torch.Tensor, device):
+    v = v.to(device)
+    return v.view(torch.int32) if v.dtype == torch.uint32 else v
+
+
+def _empty_model(args: ModelArgs, device) -> Model:
+    """Instantiate the module tree with empty parameters (nn.quantize swaps shells in the same way,
+    PIE/models/utils.py:95-111)."""
+    from . import nn as pnn
+
+    gs, bits = args.quantization["group_size"], args.quantization["bits"]
+    orig_ql, orig_qe = pnn.QuantizedLinear.__init__, pnn.QuantizedEmbedding.__init__
+
+    def ql_init(self, input_dims, output_dims, bias=True, group_size=64, bits=4, device="cuda"):
+        self.group_size, self.bits = group_size, bits
+        self.weight = torch.empty((output_dims, input_dims * bits // 32), dtype=torch.int32, device=device)
+        self.scales = torch.empty((output_dims, input_dims // group_size), dtype=torch.bfloat16, device=device)
+        self.biases = torch.empty_like(self.scales)
+
+    def qe_init(self, num_embeddings, dims, group_size=64, bits=4, device="cuda"):
+        self.group_size, self.bits, self.num_embeddings, self.dims = group_size, bits, num_embeddings, dims
+        self.weight = torch.empty((num_embeddings, dims * bits // 32), dtype=torch.int32, device=device)
+        self.scales = torch.empty((num_embeddings, dims // group_size), dtype=torch.bfloat16, device=device)
+        self.biases = torch.empty_like(self.scales)
+
+    pnn.QuantizedLinear.__init__, pnn.QuantizedEmbedding.__init__ = ql_init, qe_init
+    try:
+        return Model(args, device)
+    finally:
+        pnn.QuantizedLinear.__init__, pnn.QuantizedEmbedding.__init__ = orig_ql, orig_qe
+
+
+def save_checkpoint(path: str, args: ModelArgs, weights: dict) -> None:
+    from safetensors.torch import save_file
+
+    os.makedirs(path, exist_ok=True)
+    cfg = {k: getattr(args, k) for k in args.__dataclass_fields__}
+    with open(os.path.join(path, "config.json"), "w") as f:
+        json.dump(cfg, f, indent=1)
+    out = {k: (v.view(torch.uint32) if v.dtype == torch.int32 else v).cpu().contiguous() for k, v in weights.items()}
+    save_file(out, os.path.join(path, "model.safetensors"), metadata={"format": "mlx"})
+
+
+def load_model(path: str, device="cuda") -> Model:
+    """PIE/models/utils.py:51-125 for the Llama family."""
+    from safetensors.torch import load_file
+
+    with open(os.path.join(path, "config.json")) as f:
+        config = json.load(f)
+    files = glob.glob(os.path.join(path, "model*.safetensors"))
+    if not files:
+        raise FileNotFoundError(f"No safetensors found in {path}")
+    if config.get("model_type", "llama") != "llama":
+        raise ValueError(f"Model type {config.get('model_type')} not supported.")
+    if "quantization" not in config:
+        raise ValueError("only MLX-quantized checkpoints (config['quantization']) are on this path")
+    weights = {}
+    for wf in files:
+        weights.update(load_file(wf))
+    return build_model(ModelArgs.from_dict(config), weights, device)

@@ -117,11 +117,13 @@ int pie_add(void* out, const void* a, const void* b, long long n, void* stream) 
   if (!out || !a || !b) return PIE_ENULL;
   return cuda_status(launch_add((uint16_t*)out, (const uint16_t*)a, (const uint16_t*)b, n, (cudaStream_t)stream));
 }
-int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_t* positions_to_advance, void* stream) {
+int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_t* positions_to_advance,
+               int32_t* seq_out, int seq_ld, void* stream) {
   if (rows == 0) return PIE_OK;
   if (!out_idx || !logits) return PIE_ENULL;
   if (rows < 0 || vocab <= 0) return PIE_EINVAL_SHAPE;
-  return cuda_status(launch_argmax(out_idx, (const uint16_t*)logits, rows, vocab, positions_to_advance, (cudaStream_t)stream));
+  return cuda_status(launch_argmax(out_idx, (const uint16_t*)logits, rows, vocab, positions_to_advance, seq_out, seq_ld,
+                                   (cudaStream_t)stream));
 }
 
 }  // extern "C"

@@ -81,7 +81,7 @@ cudaError_t launch_prefill_attn(uint16_t* out, const uint16_t* q, const uint16_t
 cudaError_t launch_silu_mul(uint16_t* out, const uint16_t* g, const uint16_t* u, long long n, cudaStream_t st);
 cudaError_t launch_add(uint16_t* out, const uint16_t* a, const uint16_t* b, long long n, cudaStream_t st);
 cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vocab, int32_t* pos_adv,
-                          cudaStream_t st);
+                          int32_t* seq_out, int seq_ld, cudaStream_t st);
 
 void count_launch(int n = 1);
 

@@ -146,7 +146,7 @@ cudaError_t launch_add(uint16_t* out, const uint16_t* a, const uint16_t* b, long
 
 // ---- greedy sampler: first index of the row maximum (mx.argmax; PIE/samplers/__init__.py, temp == 0) --------
 __global__ void __launch_bounds__(1024) argmax_kernel(int32_t* out, const uint16_t* logits, int vocab,
-                                                      int32_t* pos_adv) {
+                                                      int32_t* pos_adv, int32_t* seq_out, int seq_ld) {
   __shared__ float sv[32];
   __shared__ int si[32];
   const uint16_t* row = logits + (size_t)blockIdx.x * vocab;
@@ -172,15 +172,19 @@ __global__ void __launch_bounds__(1024) argmax_kernel(int32_t* out, const uint16
     }
     if (threadIdx.x == 0) {
       out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
-      if (pos_adv) pos_adv[blockIdx.x] += 1;  // the token just sampled occupies the next cache slot
+      if (pos_adv) {  // the token just sampled occupies the next cache slot
+        const int np = pos_adv[blockIdx.x] + 1;
+        pos_adv[blockIdx.x] = np;
+        if (seq_out && np < seq_ld) seq_out[(size_t)blockIdx.x * seq_ld + np] = bi == 0x7fffffff ? 0 : bi;
+      }
     }
   }
 }
 cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vocab, int32_t* pos_adv,
-                          cudaStream_t st) {
+                          int32_t* seq_out, int seq_ld, cudaStream_t st) {
   if (rows == 0) return cudaSuccess;
   count_launch();
-  argmax_kernel<<<rows, 1024, 0, st>>>(out, logits, vocab, pos_adv);
+  argmax_kernel<<<rows, 1024, 0, st>>>(out, logits, vocab, pos_adv, seq_out, seq_ld);
   return cudaGetLastError();
 }
 

@@ -7,9 +7,9 @@ cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStre
   static size_t configured[2] = {0, 0};  // largest dynamic smem opted in so far, per instantiation
   size_t& conf = configured[bits == 4 ? 0 : 1];
   if (smem > conf) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
     if (e != cudaSuccess) return e;
-    conf = 227 * 1024;
+    conf = 224 * 1024;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)a.ntiles, (unsigned)a.ksplit, 1);

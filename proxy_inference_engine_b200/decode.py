@@ -1,0 +1,210 @@
+"""Decode engine: the generate_step loop of PIE (PIE/engine/inference_engine.py:228-297) with temp == 0, run as
+one CUDA-graph replay per token over the fused sm_100a kernels.
+
+One step (the wiring of PIE/models/llama/language.py:75-210, L == 1), 5 launches per layer:
+    h      = dequantize(embed[token])                                   QuantizedEmbedding.__call__
+    per layer:
+      qkv  = qmv_fused(rms_norm(h, w_in) ; [q_proj | k_proj | v_proj])   input_layernorm + 3 QuantizedLinear
+      q    = rope(q), cache[pos] = (rope(k), v)                         Llama3RoPE + update_and_fetch
+      o    = flash-decode(q, cache[:pos + 1])                           scaled_dot_product_attention
+      h    = h + qmv(o ; o_proj)                                        o_proj + residual
+      a    = silu(gate) * up,  (gate, up) = qmv(rms_norm(h, w_post))    post_attention_layernorm + MLP front
+      h    = h + qmv(a ; down_proj)                                     down_proj + residual
+    logits = qmv_fused(rms_norm(h, w_norm) ; lm_head)                   norm + head (tied: embed.as_linear)
+    token  = argmax(logits); positions += 1; seq[b, pos] = token        sampler, cache.offset += 1
+Token ids and positions stay on the device; the host reads the token list back when it wants it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib, ops
+from ._lib import EPI_RESADD, EPI_SILUMUL, EPI_STORE, KvLayout, QmvSeg
+from .cache import KVCache, PagedKVCache
+from .llama import Model
+from .ops import _p, _stream
+
+
+def _segs(*linears):
+    arr = (QmvSeg * len(linears))()
+    for i, l in enumerate(linears):
+        arr[i].wq, arr[i].scales, arr[i].biases = l.weight.data_ptr(), l.scales.data_ptr(), l.biases.data_ptr()
+        arr[i].N = l.weight.shape[0]
+    return arr
+
+
+class DecodeEngine:
+    def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
+                 use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2):
+        a = model.args
+        self.model, self.args, self.B, self.max_context = model, a, batch, max_context
+        self.pdl, self.use_graph = int(pdl), use_graph
+        dev = model.model.norm.weight.device
+        self.dev = dev
+        at0 = model.layers[0].self_attn
+        self.Hq, self.Hkv, self.D = at0.num_heads, at0.n_kv_heads, at0.head_dim
+        self.gs, self.bits = a.quantization["group_size"], a.quantization["bits"]
+        bf = torch.bfloat16
+        B, h = batch, a.hidden_size
+        self.tokens = torch.zeros((B,), dtype=torch.int32, device=dev)
+        self.positions = torch.zeros((B,), dtype=torch.int32, device=dev)
+        self.seq = torch.zeros((B, max_context + 1), dtype=torch.int32, device=dev)
+        self.h = torch.empty((B, h), dtype=bf, device=dev)
+        self.qkv = torch.empty((B, (self.Hq + 2 * self.Hkv) * self.D), dtype=bf, device=dev)
+        self.q = torch.empty((B, self.Hq, self.D), dtype=bf, device=dev)
+        self.attn = torch.empty((B, self.Hq * self.D), dtype=bf, device=dev)
+        self.act = torch.empty((B, a.intermediate_size), dtype=bf, device=dev)
+        self.logits = torch.empty((B, a.vocab_size), dtype=bf, device=dev)
+        # caches
+        self.paged = paged
+        if paged:
+            n_pg = (max_context + 63) // 64
+            g = torch.Generator(device="cpu").manual_seed(seed)
+            perm = torch.randperm(B * n_pg, generator=g).to(torch.int32).reshape(B, n_pg).to(dev)
+            self.page_table = perm
+            self.cache = [PagedKVCache(torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev),
+                                       torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev), perm)
+                          for _ in model.layers]
+            self.lay = [c.layout() for c in self.cache]
+            self.kbuf = [c.k_pool for c in self.cache]
+            self.vbuf = [c.v_pool for c in self.cache]
+        else:
+            self.cache = model.make_cache(max_context)
+            for c in self.cache:
+                c.reserve(B, self.Hkv, self.D, max_context, dev)
+            self.lay = [ops.kv_layout(c.keys) for c in self.cache]
+            self.kbuf = [c.keys for c in self.cache]
+            self.vbuf = [c.values for c in self.cache]
+        L = _lib.load()
+        self.L = L
+        self.nsplit = L.pie_decode_attn_pick_splits(B, self.Hq, self.Hkv, max_context)
+        nb = L.pie_decode_attn_workspace_bytes(B, self.Hq, self.D, self.nsplit)
+        self.attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
+        # per-layer segment tables (host structs must outlive the captured graph: keep references)
+        self.seg_qkv, self.seg_o, self.seg_gu, self.seg_down = [], [], [], []
+        nb = 0
+        mb = min(B, 8)
+        for ly in model.layers:
+            at, mlp = ly.self_attn, ly.mlp
+            self.seg_qkv.append(_segs(at.q_proj, at.k_proj, at.v_proj))
+            self.seg_o.append(_segs(at.o_proj))
+            self.seg_gu.append(_segs(mlp.gate_proj, mlp.up_proj))
+            self.seg_down.append(_segs(mlp.down_proj))
+        head = model.model.embed_tokens if a.tie_word_embeddings else model.lm_head
+        self.seg_head = _segs(head)
+        qd = self.Hq * self.D
+        for (n, k, dual) in (((self.Hq + 2 * self.Hkv) * self.D, h, 0), (h, qd, 0), (a.intermediate_size, h, 1),
+                             (h, a.intermediate_size, 0), (a.vocab_size, h, 0)):
+            nb = max(nb, L.pie_qmv_workspace_bytes(mb, n, k, self.bits, dual, 0))
+        self.qmv_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
+        self.graph = None
+        self.launches_per_step = 0
+
+    # ------------------------------------------------------------------------------------------------
+    def _qmv(self, out, out_ld, x, x_ld, K, segs, nseg, norm_w, epi, residual):
+        _lib.check(self.L.pie_qmv_fused(_p(out), out_ld, _p(x), x_ld, self.B, K, segs, nseg, self.gs, self.bits,
+                                        _p(norm_w), float(self.args.rms_norm_eps), epi, _p(residual), 0,
+                                        _p(self.qmv_ws), self.qmv_ws.numel(), self.pdl, _stream()), "qmv_fused")
+
+    def _step_kernels(self):
+        """Enqueue one decode step on the current stream (capturable: no sync, no allocation)."""
+        a, m, L = self.args, self.model, self.L
+        emb = m.model.embed_tokens
+        h, hid = self.h, a.hidden_size
+        _lib.check(L.pie_dequantize(_p(h), _p(emb.weight), _p(emb.scales), _p(emb.biases), _p(self.tokens), self.B,
+                                    emb.weight.shape[0], hid, self.gs, self.bits, _stream()), "embed")
+        qd = self.Hq * self.D
+        for i, ly in enumerate(m.layers):
+            self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
+                      EPI_STORE, None)
+            _lib.check(L.pie_rope_kv_append(_p(self.q), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
+                                            C.byref(self.lay[i]), _p(self.positions), _p(ly.self_attn.rope._freqs),
+                                            self.B, self.Hq, self.Hkv, self.D, _stream()), "rope_kv_append")
+            _lib.check(L.pie_decode_attn(_p(self.attn), _p(self.q), _p(self.kbuf[i]), _p(self.vbuf[i]),
+                                         C.byref(self.lay[i]), _p(self.positions), self.B, self.Hq, self.Hkv, self.D,
+                                         float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),
+                                         self.attn_ws.numel(), _stream()), "decode_attn")
+            self._qmv(h, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_RESADD, h)
+            self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2,
+                      ly.post_attention_layernorm.weight, EPI_SILUMUL, None)
+            self._qmv(h, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None,
+                      EPI_RESADD, h)
+        self._qmv(self.logits, a.vocab_size, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+        _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
+                                _p(self.seq), self.seq.shape[1], _stream()), "argmax")
+
+    def _ensure_graph(self):
+        if not self.use_graph or self.graph is not None:
+            return
+        # warm-up (also opts the kernels into their shared-memory size) on a side stream, then capture.
+        # The step mutates tokens / positions / cache: save and restore them around warm-up and capture.
+        saved = (self.tokens.clone(), self.positions.clone(), self.seq.clone())
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            n0 = ops.launch_count()
+            self._step_kernels()
+            self.launches_per_step = ops.launch_count() - n0
+            self._restore(saved)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._step_kernels()
+        self._restore(saved)
+        self.graph = g
+
+    def _restore(self, saved):
+        self.tokens.copy_(saved[0]); self.positions.copy_(saved[1]); self.seq.copy_(saved[2])
+
+    # ------------------------------------------------------------------------------------------------
+    def prefill(self, prompt_ids: torch.Tensor):
+        """Whole prompt in ONE forward (inference_engine.py:278), B rows of equal length; samples the first token."""
+        ids = prompt_ids.to(self.dev).to(torch.int32).reshape(self.B, -1)
+        Lp = ids.shape[1]
+        if Lp + 1 > self.max_context:
+            raise ValueError("prompt longer than the engine's max_context")
+        if self.paged:
+            tmp = self.model.make_cache(Lp)
+            logits = self.model(ids, cache=tmp)
+            for c, t in zip(self.cache, tmp):
+                c.offset = 0
+                c.update_and_fetch(t.keys[:, :, :Lp], t.values[:, :, :Lp])
+        else:
+            for c in self.cache:
+                c.offset = 0
+            logits = self.model(ids, cache=self.cache)
+        self.positions.fill_(Lp - 1)
+        self.seq.zero_()
+        self.seq[:, :Lp] = ids
+        self.prompt_len = Lp
+        last = logits[:, -1, :].contiguous()
+        self.logits.copy_(last)
+        ops_tok = ops.argmax(last, positions_to_advance=self.positions, seq_out=self.seq)
+        self.tokens.copy_(ops_tok)
+        return self.tokens
+
+    def step(self, n: int = 1):
+        """n decode steps; each consumes self.tokens at self.positions and samples the next token."""
+        self._ensure_graph()
+        for _ in range(n):
+            if self.graph is not None:
+                self.graph.replay()
+            else:
+                n0 = ops.launch_count()
+                self._step_kernels()
+                self.launches_per_step = ops.launch_count() - n0
+        for c in self.cache:
+            c.offset += n
+
+    def generated(self) -> torch.Tensor:
+        """Tokens sampled so far, [B, n] (device -> host copy: the sync point, inference_engine.py:202)."""
+        end = int(self.positions[0].item()) + 1
+        return self.seq[:, self.prompt_len:end].cpu()
+
+    def generate(self, prompt_ids, n_steps: int) -> torch.Tensor:
+        self.prefill(prompt_ids)
+        self.step(n_steps - 1)
+        return self.generated()
