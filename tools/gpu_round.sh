@@ -1,0 +1,21 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, the bench line, the ncu launch list and one full capture of the dominant kernel.
+# Usage (from the repo root, under gpurun):  bash tools/gpu_round.sh [tag]
+TAG=${1:-r01}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/smi.txt 2>&1
+( time timeout 1200 python -m pytest tests -m gpu -x -q ) > $OUT/pytest_gpu.log 2>&1
+echo "pytest exit $?" >> $OUT/pytest_gpu.log
+( time timeout 900 python bench.py ) > $OUT/bench.log 2> $OUT/bench.err
+echo "bench exit $?" >> $OUT/bench.err
+( time timeout 600 python bench.py --impl reference --steps 2 --warmup 1 ) > $OUT/bench_ref.log 2> $OUT/bench_ref.err
+CMD="python bench.py --steps 2 --warmup 3 --prompt 8 --no-cpu-baseline --no-kernel-timing"
+timeout 600 $CMD > $OUT/plain.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:pie:: -c 1500 \
+    --csv --log-file $OUT/launches.csv $CMD > $OUT/ncu_list.log 2>&1
+timeout 600 $CMD > $OUT/plain2.log 2>&1 &&
+timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:qmv_kernel -s 400 -c 6 \
+    -o $OUT/prof_qmv $CMD > $OUT/ncu_full.log 2>&1
+ls -la $OUT
+tail -3 $OUT/pytest_gpu.log; cat $OUT/bench.log; tail -3 $OUT/bench.err; cat $OUT/bench_ref.log
