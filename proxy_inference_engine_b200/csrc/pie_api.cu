@@ -22,33 +22,50 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 static inline bool quant_supported(int gs, int bits) { return gs == 64 && (bits == 4 || bits == 8); }
 static inline int stage_k(int bits) { return kRowBytes * 8 / bits; }
 
-struct QmvPlan { int warps, ksplit, kslice, ntiles; };
+struct QmvPlan { int warps, grid, ksplit, kslice, ks_w, ntiles, mt; };
 
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e && *e ? atoi(e) : dflt;
+}
+
+// One CTA per SM.  ksplit (cross-CTA K slices) is the smallest divisor of the chunk count for which the CTA's
+// slice of x fits beside the weight rings in shared memory; ks_w (warps per team) is the largest power of two that
+// still leaves every warp >= 4 stages per tile, raised when there are too few tiles to occupy every team.
 static QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint) {
   QmvPlan p;
-  p.warps = 4;
-  if (const char* e = getenv("PIE_QMV_WARPS")) { int w = atoi(e); if (w == 4 || w == 8) p.warps = w; }
+  p.mt = qmv_mt(M);
+  p.warps = p.mt == 4 ? 8 : 16;
+  { const int w = env_int("PIE_QMV_WARPS", 0); if (w == 4 || w == 8 || w == 16) p.warps = w; }
   p.ntiles = (int)((rows_total + (dual ? 7 : 15)) / (dual ? 8 : 16));
   const int ck = stage_k(bits), chunks = K / ck;
-  int target = 148 * 4;
-  if (const char* e = getenv("PIE_QMV_TARGET_CTAS")) { int t = atoi(e); if (t > 0) target = t; }
-  int ks = ksplit_hint > 0 ? ksplit_hint : (target + p.ntiles - 1) / p.ntiles;
-  int max_ks = chunks / p.warps; if (max_ks < 1) max_ks = 1;
-  if (ks > max_ks) ks = max_ks;
-  if (ks < 1) ks = 1;
-  // shared-memory bound on the x slice: M * kslice * 2 bytes <= 96 KB
-  const int max_slice = (96 * 1024 / (2 * (M > 0 ? M : 1))) / ck * ck;
-  int per = (chunks + ks - 1) / ks;
-  if (per * ck > max_slice) per = max_slice / ck;
-  if (per < 1) per = 1;
-  p.kslice = per * ck;
-  p.ksplit = (K + p.kslice - 1) / p.kslice;
+  const int sms = num_sms();
+  p.ksplit = 0;
+  for (int ks = ksplit_hint > 0 ? ksplit_hint : 1; ks <= chunks && ks <= sms; ++ks) {
+    if (chunks % ks) continue;
+    if (qmv_smem_bytes(M, K / ks, bits, p.warps, p.mt) <= (size_t)kQmvMaxSmem) { p.ksplit = ks; break; }
+  }
+  if (p.ksplit == 0) p.ksplit = chunks;  // cannot happen for M <= 32 (one chunk of x is <= 16 KB)
+  p.kslice = K / p.ksplit;
+  int ncta = sms / p.ksplit;
+  if (ncta > p.ntiles) ncta = p.ntiles;
+  if (ncta < 1) ncta = 1;
+  p.grid = ncta * p.ksplit;
+  const int cps = chunks / p.ksplit;  // chunks per CTA slice
+  const int min_stages = env_int("PIE_QMV_MIN_STAGES", 4);
+  int ks_w = 1;
+  while (ks_w * 2 <= p.warps && cps % (ks_w * 2) == 0 && cps / (ks_w * 2) >= min_stages) ks_w *= 2;
+  int teams_wanted = p.ntiles / ncta;  // tiles per CTA: more teams than that would idle
+  if (teams_wanted < 1) teams_wanted = 1;
+  while (p.warps / ks_w > teams_wanted && ks_w * 2 <= p.warps && cps % (ks_w * 2) == 0) ks_w *= 2;
+  { const int f = env_int("PIE_QMV_KSW", 0); if (f > 0 && f <= p.warps && p.warps % f == 0 && cps % f == 0) ks_w = f; }
+  p.ks_w = ks_w;
   return p;
 }
 static size_t qmv_ws_bytes(const QmvPlan& p) {
   if (p.ksplit <= 1) return 0;
   const size_t cnt = (((size_t)p.ntiles * 4) + 255) & ~(size_t)255;
-  return cnt + (size_t)p.ntiles * p.ksplit * 128 * sizeof(float);
+  return cnt + (size_t)p.ntiles * p.ksplit * 128 * p.mt * sizeof(float);
 }
 }  // namespace pie
 
@@ -144,13 +161,16 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
     if (!dual) p.ntiles = tile;
     const size_t need = qmv_ws_bytes(p);
     if (need > workspace_bytes || (need && !workspace)) return PIE_EWORKSPACE;
-    a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice;
+    a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice; a.ks_w = p.ks_w;
+    a.ks_w_log2 = 0; while ((1 << a.ks_w_log2) < p.ks_w) ++a.ks_w_log2;
+    a.nch = p.kslice / (stage_k(bits) * p.ks_w);
+    a.lift_mask = 0x000f000fu; a.lift_magic = 0x43004300u;
     a.x = (const uint16_t*)x + (size_t)m0 * x_ld;
     a.out = (uint16_t*)out + (size_t)m0 * out_ld;
     a.residual = residual ? (const uint16_t*)residual + (size_t)m0 * out_ld : nullptr;
     a.ws_cnt = (unsigned int*)workspace;
     a.ws_part = (float*)((uint8_t*)workspace + ((((size_t)p.ntiles * 4) + 255) & ~(size_t)255));
-    const int st = cuda_status(launch_qmv(a, bits, p.warps, pdl != 0, (cudaStream_t)stream));
+    const int st = cuda_status(launch_qmv(a, bits, p.warps, p.grid, pdl != 0, (cudaStream_t)stream));
     if (st != PIE_OK) return st;
   }
   return PIE_OK;

@@ -8,10 +8,12 @@ namespace pie {
 
 constexpr int kGroup = 64;      // the only group size on the fast path
 constexpr int kTileRows = 16;   // one mma.sync m16 tile of weight rows
-constexpr int kMaxBatch = 8;    // mma.sync n8: activation rows per qmv pass
+constexpr int kMaxBatch = 32;   // activation rows per qmv pass: up to 4 mma.sync n8 column tiles
 constexpr int kMaxSeg = 3;      // q / k / v   or   gate / up
 constexpr int kRowBytes = 128;  // bytes of one weight row per ring stage (256 q4 / 128 q8 elements)
 constexpr int kQmvStages = 4;   // per-warp cp.async ring depth
+constexpr int kQmvSlots = 2;    // exchange slots per warp for the end-of-tile hand-off (power of two)
+constexpr int kQmvMaxSmem = 227 * 1024;  // dynamic shared memory a qmv CTA may use (one CTA per SM)
 
 enum Epilogue : int { EPI_STORE = 0, EPI_RESADD = 1, EPI_SILUMUL = 2 };
 
@@ -30,8 +32,12 @@ struct QmvArgs {
   int dual;      // 1: seg[0] = gate, seg[1] = up; a tile is 8 gate rows + 8 up rows (SwiGLU epilogue)
   int M, K;
   int ntiles;
-  int ksplit;    // gridDim.y
-  int kslice;    // elements of K per split (multiple of the stage's K extent)
+  int ksplit;    // cross-CTA K slices (gridDim.x % ksplit == 0); 1 unless x does not fit in shared memory
+  int kslice;    // elements of K per slice (multiple of ks_w * the stage's K extent)
+  int ks_w;      // warps per team: a tile's K slice is cut over ks_w warps of one CTA (power of two)
+  int ks_w_log2;
+  int nch;       // stages per (warp, tile) = kslice / (stage K extent * ks_w)
+  uint32_t lift_mask, lift_magic;  // 0x000f000f, 0x43004300 (see lift4)
   const uint16_t* x;  // bf16 [M, K]
   int x_ld;
   // optional fused RMSNorm of x: x <- bf16(bf16(x * inv_rms) * norm_w)   (inv_rms computed per CTA over full K)
@@ -41,7 +47,7 @@ struct QmvArgs {
   int out_ld;
   const uint16_t* residual;  // EPI_RESADD (ld = out_ld)
   int epi;
-  float* ws_part;        // [ntiles][ksplit][128] fp32, only if ksplit > 1
+  float* ws_part;        // [ntiles][ksplit][128 * mt] fp32, only if ksplit > 1
   unsigned int* ws_cnt;  // [ntiles], zero before the first launch, self-cleaning
 };
 
@@ -52,10 +58,12 @@ struct KvLayout {
 };
 
 // ---- launchers (return cudaError_t of the launch) -------------------------------------------------
-cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStream_t st);
+cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, int grid, bool pdl, cudaStream_t st);
 cudaError_t launch_qmv_generic(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s,
                                const uint16_t* b, int M, int N, int K, int gs, int bits, cudaStream_t st);
-size_t qmv_smem_bytes(int M, int kslice, int bits, int warps);
+size_t qmv_smem_bytes(int M, int kslice, int bits, int warps, int mt);
+int qmv_mt(int M);
+int num_sms();
 
 cudaError_t launch_quantize(const void* w, int dtype, uint32_t* wq, void* s, void* b, long long rows, int K,
                             int gs, int bits, cudaStream_t st);

@@ -8,7 +8,7 @@
 namespace pie {
 
 #ifndef PIE_SPIN_LIMIT
-#define PIE_SPIN_LIMIT (1u << 28)  // ~ seconds; a healthy wait is microseconds
+#define PIE_SPIN_LIMIT (1u << 20)  // try_wait itself blocks for a while: ~ seconds in total; a healthy wait is microseconds
 #endif
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

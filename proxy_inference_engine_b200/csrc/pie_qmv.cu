@@ -35,12 +35,12 @@ struct QmvGeom {
 
 __host__ __device__ inline int qmv_xrow_bytes(int kslice) { return kslice * 2 + 16; }
 
-size_t qmv_smem_bytes(int M, int kslice, int bits, int warps) {
+size_t qmv_smem_bytes(int M, int kslice, int bits, int warps, int mt) {
   size_t xs = ((size_t)M * qmv_xrow_bytes(kslice) + 127) & ~(size_t)127;
-  size_t sumx = (size_t)(kslice / kGroup) * 8 * sizeof(float);
-  size_t red = (size_t)warps * 128 * sizeof(float);
+  size_t sumx = (size_t)(kslice / kGroup) * 8 * mt * sizeof(float);
+  size_t red = (size_t)warps * kQmvSlots * 128 * mt * sizeof(float);  // exchange slots
   size_t stage = bits == 4 ? QmvGeom<4>::STAGE_BYTES : QmvGeom<8>::STAGE_BYTES;
-  return xs + sumx + red + 128 + (size_t)warps * kQmvStages * stage;
+  return xs + sumx + red + 512 + 128 + (size_t)warps * kQmvStages * stage;
 }
 
 // ---- swizzled position (bytes within the 128-byte stage row) of 16-byte chunk c of tile row r ----------
@@ -50,18 +50,22 @@ __device__ __forceinline__ int swz_chunk(int r, int c) {
   return ((((c >> 2) ^ (r & 1)) << 2) | (c & 3)) * 16;                 // 64-byte groups, 2 rows conflict-free
 }
 
-__device__ __forceinline__ uint32_t lift4(uint32_t w, int sh) {
-  return ((w >> sh) & 0x000f000fu) | 0x43004300u;  // two bf16 values 128 + nibble
+// two bf16 values 128 + nibble: ((w >> sh) & 0x000f000f) | 0x43004300.  mask and magic arrive in registers (kernel
+// arguments) so that the and-or is ONE LOP3; as immediates ptxas needs two.
+__device__ __forceinline__ uint32_t lift4(uint32_t w, int sh, uint32_t mask, uint32_t magic) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(w >> sh), "r"(mask), "r"(magic));
+  return d;
 }
 
 // ---- stage x (optionally RMS-normalised) into shared memory in B-fragment order + per-group sums ----
 // Within every block of 16 k: q4 position 4m+i <-> k = m + 4i ; q8 position 4m+{0,1,2,3} <-> k = 4m+{0,2,1,3}.
-template <int BITS>
+template <int BITS, int MT>
 __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* sumx, float* red) {
   const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31;
   const int xrow = qmv_xrow_bytes(a.kslice);
   // fused RMSNorm (mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111): inverse rms over the FULL row
-  float inv[kMaxBatch];
+  float inv[8 * MT];
   if (a.norm_w) {
     for (int m = 0; m < a.M; ++m) {
       float ss = 0.f;
@@ -129,7 +133,7 @@ __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* 
       uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)m * xrow + blk * 32);
       dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
       dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-      if ((blk & 3) == 0) sumx[(blk >> 2) * 8 + m] = s;
+      if ((blk & 3) == 0) sumx[((blk >> 2) * MT + (m >> 3)) * 8 + (m & 7)] = s;
     }
   }
 }

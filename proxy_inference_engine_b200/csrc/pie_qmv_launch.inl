@@ -1,18 +1,33 @@
 // Launcher of the decode GEMV and the slow generic kernel for shapes off the fast path.
 namespace pie {
 
-cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStream_t st) {
-  const size_t smem = qmv_smem_bytes(a.M, a.kslice, bits, warps);
-  auto kern = bits == 4 ? qmv_kernel<4> : qmv_kernel<8>;
-  static size_t configured[2] = {0, 0};  // largest dynamic smem opted in so far, per instantiation
-  size_t& conf = configured[bits == 4 ? 0 : 1];
-  if (smem > conf) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+int qmv_mt(int M) { return M <= 8 ? 1 : (M <= 16 ? 2 : 4); }
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      n = v;
+    else
+      return 148;  // no device visible (host-side sizing calls): the B200 count
+  }
+  return n;
+}
+
+template <int BITS, int MT, bool ONECOL>
+static cudaError_t launch_qmv_t(const QmvArgs& a, int warps, int grid, bool pdl, cudaStream_t st) {
+  const size_t smem = qmv_smem_bytes(a.M, a.kslice, BITS, warps, MT);
+  static bool configured = false;  // opt in to the full 227 KB of dynamic shared memory once
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qmv_kernel<BITS, MT, ONECOL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kQmvMaxSmem);
     if (e != cudaSuccess) return e;
-    conf = 224 * 1024;
+    configured = true;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)a.ntiles, (unsigned)a.ksplit, 1);
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
   cfg.blockDim = dim3((unsigned)warps * 32, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
@@ -22,7 +37,21 @@ cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, bool pdl, cudaStre
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   count_launch();
-  return cudaLaunchKernelEx(&cfg, kern, a);
+  return cudaLaunchKernelEx(&cfg, qmv_kernel<BITS, MT, ONECOL>, a);
+}
+
+cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, int grid, bool pdl, cudaStream_t st) {
+  const int mt = qmv_mt(a.M);
+  if (bits == 4) {
+    if (a.M == 1) return launch_qmv_t<4, 1, true>(a, warps, grid, pdl, st);
+    if (mt == 1) return launch_qmv_t<4, 1, false>(a, warps, grid, pdl, st);
+    if (mt == 2) return launch_qmv_t<4, 2, false>(a, warps, grid, pdl, st);
+    return launch_qmv_t<4, 4, false>(a, warps, grid, pdl, st);
+  }
+  if (a.M == 1) return launch_qmv_t<8, 1, true>(a, warps, grid, pdl, st);
+  if (mt == 1) return launch_qmv_t<8, 1, false>(a, warps, grid, pdl, st);
+  if (mt == 2) return launch_qmv_t<8, 2, false>(a, warps, grid, pdl, st);
+  return launch_qmv_t<8, 4, false>(a, warps, grid, pdl, st);
 }
 
 // One warp per output row, any M; bits in {2,4,8}, group_size in {32,64,128}.  fp32, k-ordered per lane.

@@ -85,7 +85,7 @@ class DecodeEngine:
         # per-layer segment tables (host structs must outlive the captured graph: keep references)
         self.seg_qkv, self.seg_o, self.seg_gu, self.seg_down = [], [], [], []
         nb = 0
-        mb = min(B, 8)
+        mb = min(B, 32)
         for ly in model.layers:
             at, mlp = ly.self_attn, ly.mlp
             self.seg_qkv.append(_segs(at.q_proj, at.k_proj, at.v_proj))

@@ -147,7 +147,7 @@ def quantized_matmul(x, w, scales, biases, transpose: bool = True, group_size: i
     M = x2.shape[0]
     y = torch.empty((M, N), dtype=_BF16, device=x.device)
     L = _lib.load()
-    nb = L.pie_qmv_workspace_bytes(min(M, 8) if M else 1, N, K, bits, 0, 0) if bits in (4, 8) and group_size == 64 else 0
+    nb = L.pie_qmv_workspace_bytes(min(M, 32) if M else 1, N, K, bits, 0, 0) if bits in (4, 8) and group_size == 64 else 0
     ws = workspaces.get("qmv", nb, x.device)
     fn = L.pie_qmv if M <= 32 else L.pie_qmm
     _lib.check(fn(_p(y), _p(x2), _p(w), _p(scales), _p(biases), M, N, K, group_size, bits, _p(ws), ws.numel(),

@@ -54,7 +54,8 @@ def test_dequantize_exact_and_gather(env, bits):
 
 
 QMM_CASES = [(1, 128, 256), (2, 48, 512), (5, 33, 256), (8, 256, 1024), (9, 64, 768), (33, 128, 256),
-             (1, 3, 256), (1, 4096, 4096), (4, 1024, 14336)]
+             (1, 3, 256), (1, 4096, 4096), (4, 1024, 14336), (16, 528, 2048), (24, 96, 4096), (32, 256, 14336),
+             (70, 64, 512), (1, 6144, 4096), (2, 4720, 1024)]
 
 
 @pytest.mark.parametrize("bits", [4, 8])

@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--shapes", default="qkv,o,gate_up,down,head")
     ap.add_argument("--ksplit", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=0, help="time N launches captured in one CUDA graph (no CPU launch cost)")
+    ap.add_argument("--pdl", type=int, default=0)
     a = ap.parse_args()
     L = _lib.load()
     dev = "cuda"
@@ -56,12 +58,29 @@ def main():
         def run(i):
             segs = sets[i % copies][0]
             st = L.pie_qmv_fused(_p(out), out_n, _p(x), K, a.M, K, segs, len(Ns), 64, a.bits, _p(nw) if norm else None,
-                                 1e-5, epi, _p(out) if epi == 1 else None, a.ksplit, _p(ws), ws.numel(), 0, _stream())
+                                 1e-5, epi, _p(out) if epi == 1 else None, a.ksplit, _p(ws), ws.numel(), a.pdl, _stream())
             _lib.check(st, name)
 
         for i in range(3):
             run(i)
         torch.cuda.synchronize()
+        if a.graph:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for i in range(a.graph):
+                    run(i)
+            g.replay(); torch.cuda.synchronize()
+            ts = []
+            for _ in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1) / a.graph)
+            ts.sort()
+            med = ts[len(ts) // 2]
+            byts = per_copy + a.M * K * 2 + a.M * out_n * 2
+            res[name] = {"us": round(med * 1e3, 2), "min_us": round(ts[0] * 1e3, 2), "GBps": round(byts / med / 1e6, 1),
+                         "MB": round(byts / 1e6, 2)}
+            continue
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.iters)]
         for i, (e0, e1) in enumerate(evs):
             e0.record(); run(i); e1.record()
