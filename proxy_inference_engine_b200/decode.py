@@ -116,21 +116,29 @@ class DecodeEngine:
         _lib.check(L.pie_dequantize(_p(h), _p(emb.weight), _p(emb.scales), _p(emb.biases), _p(self.tokens), self.B,
                                     emb.weight.shape[0], hid, self.gs, self.bits, _stream()), "embed")
         qd = self.Hq * self.D
+        import os
+        skip = set(filter(None, os.environ.get("PIE_DEBUG_SKIP", "").split(",")))  # tools/bench_step_parts.py only
         for i, ly in enumerate(m.layers):
-            self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
-                      EPI_STORE, None)
-            _lib.check(L.pie_rope_kv_append(_p(self.q), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
+            if "qkv" not in skip:
+                self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
+                          EPI_STORE, None)
+            if "rope" not in skip:
+                _lib.check(L.pie_rope_kv_append(_p(self.q), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                             C.byref(self.lay[i]), _p(self.positions), _p(ly.self_attn.rope._freqs),
-                                            self.B, self.Hq, self.Hkv, self.D, _stream()), "rope_kv_append")
-            _lib.check(L.pie_decode_attn(_p(self.attn), _p(self.q), _p(self.kbuf[i]), _p(self.vbuf[i]),
+                                                self.B, self.Hq, self.Hkv, self.D, _stream()), "rope_kv_append")
+            if "attn" not in skip:
+                _lib.check(L.pie_decode_attn(_p(self.attn), _p(self.q), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                          C.byref(self.lay[i]), _p(self.positions), self.B, self.Hq, self.Hkv, self.D,
                                          float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),
                                          self.attn_ws.numel(), _stream()), "decode_attn")
-            self._qmv(h, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_RESADD, h)
-            self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2,
-                      ly.post_attention_layernorm.weight, EPI_SILUMUL, None)
-            self._qmv(h, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None,
-                      EPI_RESADD, h)
+            if "o" not in skip:
+                self._qmv(h, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_RESADD, h)
+            if "gu" not in skip:
+                self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2,
+                          ly.post_attention_layernorm.weight, EPI_SILUMUL, None)
+            if "down" not in skip:
+                self._qmv(h, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None,
+                          EPI_RESADD, h)
         self._qmv(self.logits, a.vocab_size, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
         _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
                                 _p(self.seq), self.seq.shape[1], _stream()), "argmax")
