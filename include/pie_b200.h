@@ -139,6 +139,15 @@ int pie_decode_attn(void* out, const void* q, const void* kcache, const void* vc
                     const pie_kv_layout* kv_host, const int32_t* positions, int B, int Hq, int Hkv, int D,
                     float scale, int nsplit, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- a7+a8+a9 in one launch: rotate q and k at positions[b], append k,v to the cache, flash-decode ---------------
+ * (Attention.__call__ PIE/models/llama/language.py:84-104 for L == 1).  qkv bf16 [B, (Hq + 2 Hkv) D] un-rotated, as
+ * the fused q/k/v projection writes it; out bf16 [B, Hq D].  One CTA of 16 warps per (row, kv head, pair of query
+ * heads, context split); the appended token is read from qkv, older ones from the cache.  Workspace and nsplit as
+ * for pie_decode_attn (pie_decode_step_pick_splits sizes nsplit for this kernel).                              */
+int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache, const pie_kv_layout* kv_host,
+                          const int32_t* positions, const float* freqs, int B, int Hq, int Hkv, int D, float scale,
+                          int nsplit, void* workspace, size_t workspace_bytes, int pdl, void* stream);
+
 /* ---- a10 SDPA for L > 1 with the additive causal mask of create_attention_mask (PIE/models/base.py:18-53)
  * q bf16 [B, Hq, L, D]; k,v read from the cache (T = offset + L tokens); out bf16 [B, L, Hq * D].       */
 int pie_prefill_attn(void* out, const void* q, const void* kcache, const void* vcache,
@@ -156,6 +165,54 @@ int pie_add(void* out, const void* a, const void* b, long long n, void* stream);
  * device-side token list of the engine: the sampled token is also stored at seq_out[row, new position].  */
 int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_t* positions_to_advance,
                int32_t* seq_out, int seq_ld, void* stream);
+
+
+/* ---- a12  one whole decode step (L == 1) in ONE cooperative launch ---------------------------------------
+ * Model.__call__ for a single new token per sequence (PIE/models/llama/language.py:199-210 -> LlamaModel.__call__
+ * :170-187 -> TransformerBlock.__call__ :144-154 -> Attention.__call__ :75-108 / MLP.__call__ :126-127) followed by
+ * the temp == 0 sampler and `cache.offset += 1` of generate_step (PIE/engine/inference_engine.py:282-297):
+ *   h = embed[tokens]; per layer: qkv = qmv(rms_norm(h)); rope(q,k) at positions[b]; append k,v; flash-decode;
+ *   h += qmv(attn; o); act = silu(gate)*up of qmv(rms_norm(h)); h += qmv(act; down);  logits = qmv(rms_norm(h); head);
+ *   tokens[b] = argmax(logits[b]); positions[b] += 1; seq[b, positions[b]] = tokens[b].
+ * A persistent kernel (one CTA per SM) walks the step's matrices in order: each warp keeps its cp.async weight ring
+ * streaming across the grid barriers that separate the matrices, so HBM never idles between them.  Same arithmetic,
+ * operation for operation, as the per-operator entry points above.  B <= 8 rows.
+ * Protocol: pie_decode_step_plan() (host only, no CUDA call) turns the description into `plan_host`
+ * (pie_decode_step_plan_bytes(n_layers) bytes); the caller copies it to the device once; pie_decode_step() launches.
+ * `sync_ws`: 256 device bytes, zeroed once at allocation.  attn_ws: pie_decode_step_attn_ws_bytes(), zeroed once. */
+typedef struct pie_step_layer {
+  pie_qmv_seg q, k, v, o, gate, up, down;
+  const void* input_norm;      /* input_layernorm.weight            bf16 [hidden] */
+  const void* post_norm;       /* post_attention_layernorm.weight   bf16 [hidden] */
+  void* kcache;
+  void* vcache;
+  pie_kv_layout kv;
+} pie_step_layer;
+typedef struct pie_step_model {
+  int n_layers, hidden, ffn, Hq, Hkv, D, vocab, bits, group_size;
+  float rms_eps, attn_scale;
+  const float* rope_freqs;     /* f32 [D/2], Llama3RoPE._freqs */
+  pie_qmv_seg embed;           /* embed_tokens (N = vocab) */
+  pie_qmv_seg head;            /* lm_head, or embed_tokens again when tied */
+  const void* final_norm;
+} pie_step_model;
+typedef struct pie_step_io {
+  int B;
+  int32_t* tokens;             /* [B] in: token to consume; out: token sampled */
+  int32_t* positions;          /* [B] in: cache slot of the consumed token; out: +1 */
+  int32_t* seq; int seq_ld;    /* optional token list [B, seq_ld] */
+  void *h, *qkv, *attn, *act, *logits;   /* bf16 scratch: [B,hidden] [B,(Hq+2Hkv)D] [B,Hq*D] [B,ffn] [B,vocab] */
+  void* attn_ws; size_t attn_ws_bytes; int nsplit;  /* nsplit from pie_decode_step_pick_splits */
+  void* qmv_ws; size_t qmv_ws_bytes;     /* split-K workspace of pie_qmv_fused (max over the step's matrices) */
+  unsigned long long* trace;             /* optional profiling aid: u64 [2 + 2 * (4 n_layers + 1)] receiving CTA 0's
+                                            %globaltimer at kernel start, and per matrix: input ready / matrix done */
+} pie_step_io;
+size_t pie_decode_step_plan_bytes(int n_layers);
+int pie_decode_step_pick_splits(int B, int Hq, int Hkv, int max_context);
+size_t pie_decode_step_attn_ws_bytes(int B, int Hq, int D, int nsplit);
+int pie_decode_step_plan(const pie_step_model* model, const pie_step_layer* layers, const pie_step_io* io,
+                         void* plan_host, size_t plan_bytes);
+int pie_decode_step(const void* plan_dev, const void* plan_host, size_t plan_bytes, void* sync_ws, void* stream);
 
 #ifdef __cplusplus
 }

@@ -29,6 +29,29 @@ class KvLayout(C.Structure):
                 ("page_table", C.c_void_p), ("pt_stride", C.c_int), ("page_size", C.c_int)]
 
 
+class StepLayer(C.Structure):
+    """pie_step_layer"""
+    _fields_ = [("q", QmvSeg), ("k", QmvSeg), ("v", QmvSeg), ("o", QmvSeg), ("gate", QmvSeg), ("up", QmvSeg),
+                ("down", QmvSeg), ("input_norm", C.c_void_p), ("post_norm", C.c_void_p), ("kcache", C.c_void_p),
+                ("vcache", C.c_void_p), ("kv", KvLayout)]
+
+
+class StepModel(C.Structure):
+    """pie_step_model"""
+    _fields_ = [("n_layers", C.c_int), ("hidden", C.c_int), ("ffn", C.c_int), ("Hq", C.c_int), ("Hkv", C.c_int),
+                ("D", C.c_int), ("vocab", C.c_int), ("bits", C.c_int), ("group_size", C.c_int),
+                ("rms_eps", C.c_float), ("attn_scale", C.c_float), ("rope_freqs", C.c_void_p), ("embed", QmvSeg),
+                ("head", QmvSeg), ("final_norm", C.c_void_p)]
+
+
+class StepIO(C.Structure):
+    """pie_step_io"""
+    _fields_ = [("B", C.c_int), ("tokens", C.c_void_p), ("positions", C.c_void_p), ("seq", C.c_void_p),
+                ("seq_ld", C.c_int), ("h", C.c_void_p), ("qkv", C.c_void_p), ("attn", C.c_void_p),
+                ("act", C.c_void_p), ("logits", C.c_void_p), ("attn_ws", C.c_void_p), ("attn_ws_bytes", C.c_size_t),
+                ("nsplit", C.c_int), ("qmv_ws", C.c_void_p), ("qmv_ws_bytes", C.c_size_t), ("trace", C.c_void_p)]
+
+
 _vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
 
 # name -> (restype, argtypes); must list every symbol include/pie_b200.h declares (tests check this)
@@ -51,10 +74,17 @@ SIGNATURES = {
     "pie_decode_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "pie_decode_attn_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
+    "pie_decode_attn_fused": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _sz,
+                                   _i, _vp]),
     "pie_prefill_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _i, _i, _i, _i, _i, _i, _f, _vp]),
     "pie_silu_mul": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_add": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_argmax": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
+    "pie_decode_step_plan_bytes": (_sz, [_i]),
+    "pie_decode_step_pick_splits": (_i, [_i, _i, _i, _i]),
+    "pie_decode_step_attn_ws_bytes": (_sz, [_i, _i, _i, _i]),
+    "pie_decode_step_plan": (_i, [C.POINTER(StepModel), C.POINTER(StepLayer), C.POINTER(StepIO), _vp, _sz]),
+    "pie_decode_step": (_i, [_vp, _vp, _sz, _vp, _vp]),
 }
 
 _lib = None

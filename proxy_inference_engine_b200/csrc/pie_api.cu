@@ -22,7 +22,6 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 static inline bool quant_supported(int gs, int bits) { return gs == 64 && (bits == 4 || bits == 8); }
 static inline int stage_k(int bits) { return kRowBytes * 8 / bits; }
 
-struct QmvPlan { int warps, grid, ksplit, kslice, ks_w, ntiles, mt; };
 
 static int env_int(const char* name, int dflt) {
   const char* e = getenv(name);
@@ -32,18 +31,21 @@ static int env_int(const char* name, int dflt) {
 // One CTA per SM.  ksplit (cross-CTA K slices) is the smallest divisor of the chunk count for which the CTA's
 // slice of x fits beside the weight rings in shared memory; ks_w (warps per team) is the largest power of two that
 // still leaves every warp >= 4 stages per tile, raised when there are too few tiles to occupy every team.
-static QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint) {
+QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint, int force_warps) {
   QmvPlan p;
   p.mt = qmv_mt(M);
   p.warps = p.mt == 4 ? 8 : 16;
-  { const int w = env_int("PIE_QMV_WARPS", 0); if (w == 4 || w == 8 || w == 16) p.warps = w; }
+  { const int w = env_int("PIE_QMV_WARPS", 0); if (w == 4 || w == 8 || (w == 16 && p.mt < 4)) p.warps = w; }
+  if (force_warps) p.warps = force_warps;
   p.ntiles = (int)((rows_total + (dual ? 7 : 15)) / (dual ? 8 : 16));
   const int ck = stage_k(bits), chunks = K / ck;
   const int sms = num_sms();
+  // the fused decode step keeps per-thread producer words and a little static shared memory beside the GEMV's own
+  const size_t reserve = force_warps ? (size_t)force_warps * 32 * kQmvProdWords * 4 + 2048 : 0;
   p.ksplit = 0;
   for (int ks = ksplit_hint > 0 ? ksplit_hint : 1; ks <= chunks && ks <= sms; ++ks) {
     if (chunks % ks) continue;
-    if (qmv_smem_bytes(M, K / ks, bits, p.warps, p.mt) <= (size_t)kQmvMaxSmem) { p.ksplit = ks; break; }
+    if (qmv_smem_bytes(M, K / ks, bits, p.warps, p.mt) + reserve <= (size_t)kQmvMaxSmem) { p.ksplit = ks; break; }
   }
   if (p.ksplit == 0) p.ksplit = chunks;  // cannot happen for M <= 32 (one chunk of x is <= 16 KB)
   p.kslice = K / p.ksplit;
@@ -62,11 +64,66 @@ static QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, 
   p.ks_w = ks_w;
   return p;
 }
-static size_t qmv_ws_bytes(const QmvPlan& p) {
+size_t qmv_ws_bytes(const QmvPlan& p) {
   if (p.ksplit <= 1) return 0;
   const size_t cnt = (((size_t)p.ntiles * 4) + 255) & ~(size_t)255;
   return cnt + (size_t)p.ntiles * p.ksplit * 128 * p.mt * sizeof(float);
 }
+
+// Validate one fused GEMV and fill its launch descriptor for activation rows m0 .. m0 + mb - 1 (mb <= kMaxBatch).
+// force_warps != 0 pins the warp count (the fused decode step runs every matrix with the same CTA shape).
+int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x, int x_ld, int m0, int mb, int K,
+                   const pie_qmv_seg* segs, int nseg, int group_size, int bits, const void* norm_weight, float eps,
+                   int epilogue, const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes,
+                   int force_warps) {
+  if (!out || !x || !segs) return PIE_ENULL;
+  if (!quant_supported(group_size, bits)) return PIE_EUNSUPPORTED;
+  if (nseg < 1 || nseg > kMaxSeg || mb <= 0 || mb > kMaxBatch || K <= 0 || K % group_size != 0) return PIE_EINVAL_SHAPE;
+  if (K % stage_k(bits) != 0 || x_ld % 8 != 0 || x_ld < K) return PIE_EUNSUPPORTED;
+  if (epilogue < PIE_EPI_STORE || epilogue > PIE_EPI_SILUMUL) return PIE_EINVAL_SHAPE;
+  if (epilogue == PIE_EPI_RESADD && !residual) return PIE_ENULL;
+  const int dual = epilogue == PIE_EPI_SILUMUL;
+  if (dual && (nseg != 2 || segs[0].N != segs[1].N)) return PIE_EINVAL_SHAPE;
+  if (!aligned16(x) || (norm_weight && !aligned16(norm_weight))) return PIE_EALIGN;
+  memset(&a, 0, sizeof(a));
+  long long rows_total = 0;
+  int tile = 0, off = 0;
+  for (int i = 0; i < nseg; ++i) {
+    if (!segs[i].wq || !segs[i].scales || !segs[i].biases) return PIE_ENULL;
+    if (segs[i].N <= 0) return PIE_EINVAL_SHAPE;
+    if (!aligned16(segs[i].wq) || (reinterpret_cast<uintptr_t>(segs[i].scales) & 7) ||
+        (reinterpret_cast<uintptr_t>(segs[i].biases) & 7)) return PIE_EALIGN;
+    a.seg[i].wq = segs[i].wq;
+    a.seg[i].scales = (const uint16_t*)segs[i].scales;
+    a.seg[i].biases = (const uint16_t*)segs[i].biases;
+    a.seg[i].N = segs[i].N;
+    a.seg[i].tile0 = tile;
+    a.seg[i].out_off = off;
+    tile += (segs[i].N + 15) / 16;
+    off += segs[i].N;
+    rows_total += segs[i].N;
+  }
+  if (dual) rows_total = segs[0].N;
+  if (out_ld < (dual ? segs[0].N : off)) return PIE_EINVAL_SHAPE;
+  a.nseg = nseg; a.dual = dual; a.K = K; a.x_ld = x_ld;
+  a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
+  a.out_ld = out_ld; a.epi = epilogue;
+  p = plan_qmv(mb, rows_total, K, bits, dual, ksplit_hint, force_warps);
+  if (!dual) p.ntiles = tile;
+  const size_t need = qmv_ws_bytes(p);
+  if (need > workspace_bytes || (need && !workspace)) return PIE_EWORKSPACE;
+  a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice; a.ks_w = p.ks_w;
+  a.ks_w_log2 = 0; while ((1 << a.ks_w_log2) < p.ks_w) ++a.ks_w_log2;
+  a.nch = p.kslice / (stage_k(bits) * p.ks_w);
+  a.lift_mask = 0x000f000fu; a.lift_magic = 0x43004300u;
+  a.x = (const uint16_t*)x + (size_t)m0 * x_ld;
+  a.out = (uint16_t*)out + (size_t)m0 * out_ld;
+  a.residual = residual ? (const uint16_t*)residual + (size_t)m0 * out_ld : nullptr;
+  a.ws_cnt = (unsigned int*)workspace;
+  a.ws_part = (float*)((uint8_t*)workspace + ((((size_t)p.ntiles * 4) + 255) & ~(size_t)255));
+  return PIE_OK;
+}
+int status_of(cudaError_t e) { return cuda_status(e); }
 }  // namespace pie
 
 using namespace pie;
@@ -113,7 +170,7 @@ int pie_dequantize(void* out, const uint32_t* wq, const void* scales, const void
 
 size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int dual, int ksplit_hint) {
   if (M <= 0 || n_total <= 0 || K <= 0 || (bits != 4 && bits != 8) || K % stage_k(bits) != 0) return 0;
-  QmvPlan p = plan_qmv(M > kMaxBatch ? kMaxBatch : M, n_total, K, bits, dual, ksplit_hint);
+  QmvPlan p = plan_qmv(M > kMaxBatch ? kMaxBatch : M, n_total, K, bits, dual, ksplit_hint, 0);
   p.ntiles += kMaxSeg;  // segments are tiled separately: up to one ragged tile each
   return qmv_ws_bytes(p);
 }
@@ -122,54 +179,13 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
                   int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
                   int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
   if (M == 0) return PIE_OK;
-  if (!out || !x || !segs) return PIE_ENULL;
-  if (!quant_supported(group_size, bits)) return PIE_EUNSUPPORTED;
-  if (nseg < 1 || nseg > kMaxSeg || M < 0 || K <= 0 || K % group_size != 0) return PIE_EINVAL_SHAPE;
-  if (K % stage_k(bits) != 0 || x_ld % 8 != 0 || x_ld < K) return PIE_EUNSUPPORTED;
-  if (epilogue < PIE_EPI_STORE || epilogue > PIE_EPI_SILUMUL) return PIE_EINVAL_SHAPE;
-  if (epilogue == PIE_EPI_RESADD && !residual) return PIE_ENULL;
-  const int dual = epilogue == PIE_EPI_SILUMUL;
-  if (dual && (nseg != 2 || segs[0].N != segs[1].N)) return PIE_EINVAL_SHAPE;
-  if (!aligned16(x) || (norm_weight && !aligned16(norm_weight))) return PIE_EALIGN;
-  QmvArgs a;
-  memset(&a, 0, sizeof(a));
-  long long rows_total = 0;
-  int tile = 0, off = 0;
-  for (int i = 0; i < nseg; ++i) {
-    if (!segs[i].wq || !segs[i].scales || !segs[i].biases) return PIE_ENULL;
-    if (segs[i].N <= 0) return PIE_EINVAL_SHAPE;
-    if (!aligned16(segs[i].wq) || (reinterpret_cast<uintptr_t>(segs[i].scales) & 7) ||
-        (reinterpret_cast<uintptr_t>(segs[i].biases) & 7)) return PIE_EALIGN;
-    a.seg[i].wq = segs[i].wq;
-    a.seg[i].scales = (const uint16_t*)segs[i].scales;
-    a.seg[i].biases = (const uint16_t*)segs[i].biases;
-    a.seg[i].N = segs[i].N;
-    a.seg[i].tile0 = tile;
-    a.seg[i].out_off = off;
-    tile += (segs[i].N + 15) / 16;
-    off += segs[i].N;
-    rows_total += segs[i].N;
-  }
-  if (dual) rows_total = segs[0].N;
-  if (out_ld < (dual ? segs[0].N : off)) return PIE_EINVAL_SHAPE;
-  a.nseg = nseg; a.dual = dual; a.K = K; a.x_ld = x_ld;
-  a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
-  a.out_ld = out_ld; a.epi = epilogue;
   for (int m0 = 0; m0 < M; m0 += kMaxBatch) {
     const int mb = M - m0 < kMaxBatch ? M - m0 : kMaxBatch;
-    QmvPlan p = plan_qmv(mb, rows_total, K, bits, dual, ksplit_hint);
-    if (!dual) p.ntiles = tile;
-    const size_t need = qmv_ws_bytes(p);
-    if (need > workspace_bytes || (need && !workspace)) return PIE_EWORKSPACE;
-    a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice; a.ks_w = p.ks_w;
-    a.ks_w_log2 = 0; while ((1 << a.ks_w_log2) < p.ks_w) ++a.ks_w_log2;
-    a.nch = p.kslice / (stage_k(bits) * p.ks_w);
-    a.lift_mask = 0x000f000fu; a.lift_magic = 0x43004300u;
-    a.x = (const uint16_t*)x + (size_t)m0 * x_ld;
-    a.out = (uint16_t*)out + (size_t)m0 * out_ld;
-    a.residual = residual ? (const uint16_t*)residual + (size_t)m0 * out_ld : nullptr;
-    a.ws_cnt = (unsigned int*)workspace;
-    a.ws_part = (float*)((uint8_t*)workspace + ((((size_t)p.ntiles * 4) + 255) & ~(size_t)255));
+    QmvArgs a;
+    QmvPlan p;
+    const int st0 = build_qmv_args(a, p, out, out_ld, x, x_ld, m0, mb, K, segs, nseg, group_size, bits, norm_weight, eps,
+                                   epilogue, residual, ksplit_hint, workspace, workspace_bytes, 0);
+    if (st0 != PIE_OK) return st0;
     const int st = cuda_status(launch_qmv(a, bits, p.warps, p.grid, pdl != 0, (cudaStream_t)stream));
     if (st != PIE_OK) return st;
   }

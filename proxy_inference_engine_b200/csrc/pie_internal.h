@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/pie_b200.h"
+
 namespace pie {
 
 constexpr int kGroup = 64;      // the only group size on the fast path
@@ -13,6 +15,8 @@ constexpr int kMaxSeg = 3;      // q / k / v   or   gate / up
 constexpr int kRowBytes = 128;  // bytes of one weight row per ring stage (256 q4 / 128 q8 elements)
 constexpr int kQmvStages = 4;   // per-warp cp.async ring depth
 constexpr int kQmvSlots = 2;    // exchange slots per warp for the end-of-tile hand-off (power of two)
+constexpr int kQmvBarBytes = 512;  // mbarriers at the head of a qmv CTA's shared memory (63 barriers + a live count)
+constexpr int kQmvProdWords = 8;   // per-thread producer words a fused caller parks in shared memory between stages
 constexpr int kQmvMaxSmem = 227 * 1024;  // dynamic shared memory a qmv CTA may use (one CTA per SM)
 
 enum Epilogue : int { EPI_STORE = 0, EPI_RESADD = 1, EPI_SILUMUL = 2 };
@@ -92,5 +96,14 @@ cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vo
                           int32_t* seq_out, int seq_ld, cudaStream_t st);
 
 void count_launch(int n = 1);
+
+struct QmvPlan { int warps, grid, ksplit, kslice, ks_w, ntiles, mt; };
+QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint, int force_warps);
+size_t qmv_ws_bytes(const QmvPlan& p);
+int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x, int x_ld, int m0, int mb, int K,
+                   const pie_qmv_seg* segs, int nseg, int group_size, int bits, const void* norm_weight, float eps,
+                   int epilogue, const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes,
+                   int force_warps);
+int status_of(cudaError_t e);  // cudaError_t -> pie_status, recording the error string
 
 }  // namespace pie

@@ -1,4 +1,4 @@
-  // ---- body of qmv_kernel (included inside the function by pie_qmv_main.inl): consume the ring ----------
+  // ---- body of qmv_kernel (included inside the function by pie_qmv_body.cuh): consume the ring ----------
   float y[MT][4];
 #pragma unroll
   for (int mt = 0; mt < MT; ++mt) { y[mt][0] = y[mt][1] = y[mt][2] = y[mt][3] = 0.f; }
@@ -37,25 +37,24 @@
             const int m = mt * 8 + 2 * t + (q & 1), n = nbase + g + (q >> 1) * 8;
             res_raw[mt][q] = 0;
             if (m < a.M && n < a.seg[sidx].N && !(ONECOL && (q & 1)))
-              res_raw[mt][q] = a.residual[(size_t)m * a.out_ld + a.seg[sidx].out_off + n];
+              res_raw[mt][q] = COHERENT ? (uint32_t)ldcg16(a.residual + (size_t)m * a.out_ld + a.seg[sidx].out_off + n)
+                                        : (uint32_t)a.residual[(size_t)m * a.out_ld + a.seg[sidx].out_off + n];
           }
       }
     }
     const uint32_t sbase = ring_s + c_soff;
     const uint32_t sb = sbase + sboff;
-    float sc[2][G::GPC], bi[2][G::GPC];
+    // packed bf16 scales / biases of tile rows g (index 0) and g + 8 (index 1): unpacked per group, not up front
+    uint32_t scp[2][2], bip[2][2];
     if (BITS == 4) {
-      uint2 s0 = lds64(sb), s1 = lds64(sb + 64);
-      uint2 b0 = lds64(sb + G::SB_BYTES), b1 = lds64(sb + G::SB_BYTES + 64);
-      sc[0][0] = bf16lo(s0.x); sc[0][1] = bf16hi(s0.x); sc[0][2 % G::GPC] = bf16lo(s0.y); sc[0][3 % G::GPC] = bf16hi(s0.y);
-      sc[1][0] = bf16lo(s1.x); sc[1][1] = bf16hi(s1.x); sc[1][2 % G::GPC] = bf16lo(s1.y); sc[1][3 % G::GPC] = bf16hi(s1.y);
-      bi[0][0] = bf16lo(b0.x); bi[0][1] = bf16hi(b0.x); bi[0][2 % G::GPC] = bf16lo(b0.y); bi[0][3 % G::GPC] = bf16hi(b0.y);
-      bi[1][0] = bf16lo(b1.x); bi[1][1] = bf16hi(b1.x); bi[1][2 % G::GPC] = bf16lo(b1.y); bi[1][3 % G::GPC] = bf16hi(b1.y);
+      const uint2 s0 = lds64(sb), s1 = lds64(sb + 64);
+      const uint2 b0 = lds64(sb + G::SB_BYTES), b1 = lds64(sb + G::SB_BYTES + 64);
+      scp[0][0] = s0.x; scp[0][1] = s0.y; scp[1][0] = s1.x; scp[1][1] = s1.y;
+      bip[0][0] = b0.x; bip[0][1] = b0.y; bip[1][0] = b1.x; bip[1][1] = b1.y;
     } else {
-      uint32_t s0 = lds32(sb), s1 = lds32(sb + 32);
-      uint32_t b0 = lds32(sb + G::SB_BYTES), b1 = lds32(sb + G::SB_BYTES + 32);
-      sc[0][0] = bf16lo(s0); sc[0][1] = bf16hi(s0); sc[1][0] = bf16lo(s1); sc[1][1] = bf16hi(s1);
-      bi[0][0] = bf16lo(b0); bi[0][1] = bf16hi(b0); bi[1][0] = bf16lo(b1); bi[1][1] = bf16hi(b1);
+      scp[0][0] = lds32(sb); scp[1][0] = lds32(sb + 32);
+      bip[0][0] = lds32(sb + G::SB_BYTES); bip[1][0] = lds32(sb + G::SB_BYTES + 32);
+      scp[0][1] = scp[1][1] = bip[0][1] = bip[1][1] = 0;
     }
 #pragma unroll
     for (int j = 0; j < G::GPC; ++j) {
@@ -107,14 +106,18 @@
           for (int q = 0; q < 4; ++q) acc[mt][q] = fmaf(16.f, hi[mt][q], acc[mt][q]);
         off = 128.f + 2048.f;
       }
-      const float bb0 = fmaf(-off, sc[0][j], bi[0][j]), bb1 = fmaf(-off, sc[1][j], bi[1][j]);
+      const float sc0 = j & 1 ? bf16hi(scp[0][j >> 1]) : bf16lo(scp[0][j >> 1]);
+      const float sc1 = j & 1 ? bf16hi(scp[1][j >> 1]) : bf16lo(scp[1][j >> 1]);
+      const float bi0 = j & 1 ? bf16hi(bip[0][j >> 1]) : bf16lo(bip[0][j >> 1]);
+      const float bi1 = j & 1 ? bf16hi(bip[1][j >> 1]) : bf16lo(bip[1][j >> 1]);
+      const float bb0 = fmaf(-off, sc0, bi0), bb1 = fmaf(-off, sc1, bi1);
 #pragma unroll
       for (int mt = 0; mt < MT; ++mt) {
-        y[mt][0] = fmaf(bb0, sx[mt].x, fmaf(sc[0][j], acc[mt][0], y[mt][0]));
-        y[mt][2] = fmaf(bb1, sx[mt].x, fmaf(sc[1][j], acc[mt][2], y[mt][2]));
+        y[mt][0] = fmaf(bb0, sx[mt].x, fmaf(sc0, acc[mt][0], y[mt][0]));
+        y[mt][2] = fmaf(bb1, sx[mt].x, fmaf(sc1, acc[mt][2], y[mt][2]));
         if (!ONECOL) {
-          y[mt][1] = fmaf(bb0, sx[mt].y, fmaf(sc[0][j], acc[mt][1], y[mt][1]));
-          y[mt][3] = fmaf(bb1, sx[mt].y, fmaf(sc[1][j], acc[mt][3], y[mt][3]));
+          y[mt][1] = fmaf(bb0, sx[mt].y, fmaf(sc0, acc[mt][1], y[mt][1]));
+          y[mt][3] = fmaf(bb1, sx[mt].y, fmaf(sc1, acc[mt][3], y[mt][3]));
         }
       }
     }

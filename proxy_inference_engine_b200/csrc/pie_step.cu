@@ -1,0 +1,621 @@
+// One whole decode step (L == 1) as ONE persistent cooperative kernel, sm_100a.
+//
+// Replaces, for a single new token per sequence, Model.__call__ (PIE/models/llama/language.py:199-210) with everything
+// under it -- LlamaModel.__call__ :170-187, TransformerBlock.__call__ :144-154, Attention.__call__ :75-108,
+// MLP.__call__ :126-127, QuantizedEmbedding.__call__ (MLX/python/mlx/nn/layers/quantized.py:100-107) -- and the
+// temp == 0 sampler + `cache.offset += 1` of generate_step (PIE/engine/inference_engine.py:282-297).
+//
+// Why one kernel: at batch 1 a layer's matrices are 9..66 MB, i.e. 1.5..10 us of HBM time each, while a kernel
+// boundary costs ~5 us of drain + launch + pipeline ramp.  Here one CTA per SM walks the step's matrices in order
+// (5 per layer); every warp issues the first ring stages of the NEXT matrix before it enters the grid barrier that
+// ends the current one, so the weight stream never stops at a matrix boundary.  Between q/k/v and o_proj the same
+// CTAs run RoPE + KV append + split-K flash-decode attention (o_proj's weights are already in flight).
+// The GEMV itself is qmv_body (pie_qmv_body.cuh): identical arithmetic to the per-operator entry points.
+#include "pie_internal.h"
+#include "pie_ptx.cuh"
+#include "pie_qmv_body.cuh"
+
+#include <cstring>
+
+namespace pie {
+
+enum StepPre : int { PRE_BARRIER = 0, PRE_EMBED = 1, PRE_ATTN = 2 };
+
+struct StepPhase {
+  QmvArgs q;
+  int pre;
+  int pad_;
+  // PRE_ATTN: attention of this layer, between the q/k/v matrix and o_proj
+  const uint16_t* qkv;   // bf16 [B, (Hq + 2 Hkv) D], un-rotated
+  uint16_t* attn_out;    // bf16 [B, Hq D]
+  uint16_t* kc;
+  uint16_t* vc;
+  KvLayout kv;
+};
+
+struct StepArgs {
+  const StepPhase* phases;
+  int nphases;
+  int B, Hq, Hkv, D, R, rg, nsplit;
+  float scale_log2e;
+  const float* freqs;
+  int32_t* pos;
+  float* attn_part;        // [B * Hq][nsplit][D + 2]
+  unsigned int* attn_cnt;  // [B * Hkv * rg]
+  // embedding gather
+  const uint32_t* e_wq;
+  const uint16_t* e_s;
+  const uint16_t* e_b;
+  int32_t* tokens;
+  int table_rows, hidden;
+  uint16_t* h;
+  // sampler
+  const uint16_t* logits;
+  int vocab;
+  int32_t* seq;
+  int seq_ld;
+  unsigned int* bar;  // [0] arrivals, [1] generation
+  unsigned long long* trace;
+};
+
+struct StepHeader {  // head of the host/device plan buffer
+  uint32_t magic, bits, grid, smem, onecol, nphases, plan_bytes, pad_;
+  StepArgs args;  // args.phases is patched at launch
+};
+constexpr uint32_t kStepMagic = 0x50494553u;
+constexpr int kStepWarps = 16;
+
+// ---- grid-wide barrier: arrivals counter + generation word; leaves the counter at zero --------------------------
+__device__ __forceinline__ void grid_barrier(unsigned int* bar) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int gen = ld_acquire_gpu(bar + 1);
+    __threadfence();
+    if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+      atomicExch(bar, 0u);
+      __threadfence();
+      red_release_gpu_add(bar + 1, 1u);
+    } else {
+      while (ld_acquire_gpu(bar + 1) == gen) {}
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ size_t step_kv_addr(const KvLayout& kv, int b, int h, int t) {
+  if (kv.page_table) {
+    const int page = __ldg(kv.page_table + (size_t)b * kv.pt_stride + t / kv.page_size);
+    return ((size_t)page * kv.page_size + t % kv.page_size) * kv.tok_stride + (size_t)h * kv.head_stride;
+  }
+  return (size_t)b * kv.batch_stride + (size_t)h * kv.head_stride + (size_t)t * kv.tok_stride;
+}
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+  f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// Rotate one head row held 8-lanes-wide (lane `sub` owns elements 8 sub + 64 c + j, c < C, j < 8) exactly like
+// rope_kv_append_kernel (pie_rope_kv.cu): non-traditional pairs (i, i + D/2), fp32, each product rounded, bf16 result.
+// sn / cs: sin / cos of this lane's 8 pair indices.
+template <int C>
+__device__ __forceinline__ void rope_row(float* v, const float* sn, const float* cs, int sub) {
+  if (C == 2) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x1 = v[j], x2 = v[8 + j];
+      v[j] = bfround(__fsub_rn(__fmul_rn(x1, cs[j]), __fmul_rn(x2, sn[j])));
+      v[8 + j] = bfround(__fadd_rn(__fmul_rn(x1, sn[j]), __fmul_rn(x2, cs[j])));
+    }
+  } else {  // D == 64: the pair partner lives 4 lanes away
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float other = __shfl_xor_sync(0xffffffffu, v[j], 4);
+      const float x1 = sub < 4 ? v[j] : other, x2 = sub < 4 ? other : v[j];
+      v[j] = sub < 4 ? bfround(__fsub_rn(__fmul_rn(x1, cs[j]), __fmul_rn(x2, sn[j])))
+                     : bfround(__fadd_rn(__fmul_rn(x1, sn[j]), __fmul_rn(x2, cs[j])));
+    }
+  }
+}
+
+// RoPE (a7) + KV append (a8) + split-K flash-decode (a9) for one layer, spread over the whole grid.
+// Unit = (batch row, kv head, query-head group of R, split of the context); a CTA's 16 warps take 4 tokens each per
+// round.  The token being appended is taken from the q/k/v projection output (rotated in registers and written to
+// the cache by the rgi == 0 unit); older tokens come from the cache.  Split partials are merged in split order by
+// the last unit to arrive, as in decode_attn_kernel (pie_attn.cu).
+template <int D, int R>
+__device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag) {
+  constexpr int C = D / 64, E = 8 * C, PW = D + 2, NW = kStepWarps;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, tg = lane >> 3;
+  const int units = s.B * s.Hkv * s.rg * s.nsplit;
+  const int qkv_ld = (s.Hq + 2 * s.Hkv) * D;
+  for (int u = blockIdx.x; u < units; u += gridDim.x) {
+    const int split = u % s.nsplit;
+    int rest = u / s.nsplit;
+    const int rgi = rest % s.rg; rest /= s.rg;
+    const int kvh = rest % s.Hkv;
+    const int b = rest / s.Hkv;
+    const int qh0 = kvh * (s.rg * R) + rgi * R;
+    const int p = s.pos[b], ctx = p + 1;
+    const int per = (ctx + s.nsplit - 1) / s.nsplit;
+    const int t0 = split * per, t1 = min(ctx, t0 + per);
+    const size_t rec0 = ((size_t)b * s.Hq + qh0) * s.nsplit;
+    if (t0 < t1) {
+      float sn[8], cs[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = (C == 2 ? 8 * sub : 8 * (sub & 3)) + j;
+        sincosf((float)p * (1.0f / __ldg(s.freqs + i)), &sn[j], &cs[j]);
+      }
+      const uint16_t* row = P.qkv + (size_t)b * qkv_ld;
+      float q[R][E];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint4* qp = reinterpret_cast<const uint4*>(row + (size_t)(qh0 + r) * D);
+#pragma unroll
+        for (int c = 0; c < C; ++c) unpack8(ldcg128(qp + sub + 8 * c), &q[r][8 * c]);
+        rope_row<C>(q[r], sn, cs, sub);
+#pragma unroll
+        for (int e = 0; e < E; ++e) q[r][e] *= s.scale_log2e;
+      }
+      float m[R], l[R], acc[R][E];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        m[r] = -INFINITY; l[r] = 0.f;
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[r][e] = 0.f;
+      }
+      for (int tb = t0 + warp * 4; tb < t1; tb += NW * 4) {  // warp-uniform trip count; tail lanes idle
+        const int t = tb + tg;
+        const bool ok = t < t1;
+        float kf[E], vf[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
+        const bool fresh = ok && t == p;  // the token of this step: not in the cache yet
+        uint4 kr[C], vr[C];
+        if (ok) {
+          const size_t off = step_kv_addr(P.kv, b, kvh, t);
+          const uint4* kp = fresh ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + kvh) * D)
+                                  : reinterpret_cast<const uint4*>(P.kc + off);
+          const uint4* vp = fresh ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + s.Hkv + kvh) * D)
+                                  : reinterpret_cast<const uint4*>(P.vc + off);
+#pragma unroll
+          for (int c = 0; c < C; ++c) { kr[c] = ldcg128(kp + sub + 8 * c); vr[c] = ldcg128(vp + sub + 8 * c); }
+#pragma unroll
+          for (int c = 0; c < C; ++c) { unpack8(kr[c], &kf[8 * c]); unpack8(vr[c], &vf[8 * c]); }
+        }
+        // the rotation of the fresh key needs its 8-lane group converged (D == 64 exchanges lanes): do it warp-wide
+        if (__any_sync(0xffffffffu, fresh)) {
+          float kt[E];
+#pragma unroll
+          for (int e = 0; e < E; ++e) kt[e] = kf[e];
+          rope_row<C>(kt, sn, cs, sub);
+          if (fresh) {
+#pragma unroll
+            for (int e = 0; e < E; ++e) kf[e] = kt[e];
+            if (rgi == 0) {
+              const size_t off = step_kv_addr(P.kv, b, kvh, t);
+              uint4* kd = reinterpret_cast<uint4*>(P.kc + off);
+              uint4* vd = reinterpret_cast<uint4*>(P.vc + off);
+#pragma unroll
+              for (int c = 0; c < C; ++c) { kd[sub + 8 * c] = pack8(&kf[8 * c]); vd[sub + 8 * c] = vr[c]; }
+            }
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          float sc = 0.f;
+#pragma unroll
+          for (int e = 0; e < E; ++e) sc = fmaf(q[r][e], kf[e], sc);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+          sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+          if (ok) {
+            const float mn = fmaxf(m[r], sc);
+            const float corr = exp2f(m[r] - mn), pr = exp2f(sc - mn);
+            l[r] = l[r] * corr + pr;
+#pragma unroll
+            for (int e = 0; e < E; ++e) acc[r][e] = fmaf(pr, vf[e], acc[r][e] * corr);
+            m[r] = mn;
+          }
+        }
+      }
+      // merge the 4 token slots of the warp (lanes with equal `sub` hold the same feature slice)
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const float mo = __shfl_xor_sync(0xffffffffu, m[r], o), lo = __shfl_xor_sync(0xffffffffu, l[r], o);
+          const float mn = fmaxf(m[r], mo);
+          const float ca = mn == -INFINITY ? 0.f : exp2f(m[r] - mn), cb = mn == -INFINITY ? 0.f : exp2f(mo - mn);
+          l[r] = l[r] * ca + lo * cb;
+#pragma unroll
+          for (int e = 0; e < E; ++e) acc[r][e] = acc[r][e] * ca + __shfl_xor_sync(0xffffffffu, acc[r][e], o) * cb;
+          m[r] = mn;
+        }
+      }
+      if (tg == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          float* rec = scratch + ((size_t)warp * R + r) * PW;
+#pragma unroll
+          for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) rec[(sub + 8 * c) * 8 + j] = acc[r][8 * c + j];
+          if (sub == 0) { rec[D] = m[r]; rec[D + 1] = l[r]; }
+        }
+      }
+    }
+    __syncthreads();
+    // merge the warps; thread -> (r, d).  An empty split leaves (m, l) = (-inf, 0).
+    for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
+      const int r = i / D, d = i % D;
+      float mn = -INFINITY, lt = 0.f, at = 0.f;
+      if (t0 < t1) {
+        for (int w = 0; w < NW; ++w) mn = fmaxf(mn, scratch[((size_t)w * R + r) * PW + D]);
+        for (int w = 0; w < NW; ++w) {
+          const float* rec = scratch + ((size_t)w * R + r) * PW;
+          const float cw = rec[D] == -INFINITY ? 0.f : exp2f(rec[D] - mn);
+          lt += rec[D + 1] * cw;
+          at += rec[d] * cw;
+        }
+      }
+      if (s.nsplit == 1) {
+        P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+      } else {
+        float* rec = s.attn_part + (rec0 + (size_t)r * s.nsplit + split) * PW;
+        rec[d] = at;
+        if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
+      }
+    }
+    if (s.nsplit > 1) {
+      __threadfence();
+      __syncthreads();
+      const int cidx = (b * s.Hkv + kvh) * s.rg + rgi;
+      if (threadIdx.x == 0) *s_flag = (atomicAdd(&s.attn_cnt[cidx], 1u) == (unsigned)s.nsplit - 1);
+      __syncthreads();
+      if (*s_flag) {
+        __threadfence();
+        for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
+          const int r = i / D, d = i % D;
+          const float* rec = s.attn_part + (rec0 + (size_t)r * s.nsplit) * PW;
+          float mn = -INFINITY;
+          for (int sp = 0; sp < s.nsplit; ++sp) mn = fmaxf(mn, ldcg_f32(rec + (size_t)sp * PW + D));
+          float lt = 0.f, at = 0.f;
+          for (int sp = 0; sp < s.nsplit; ++sp) {
+            const float ms = ldcg_f32(rec + (size_t)sp * PW + D);
+            const float cw = ms == -INFINITY ? 0.f : exp2f(ms - mn);
+            lt += ldcg_f32(rec + (size_t)sp * PW + D + 1) * cw;
+            at += ldcg_f32(rec + (size_t)sp * PW + d) * cw;
+          }
+          P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+        }
+        if (threadIdx.x == 0) s.attn_cnt[cidx] = 0;
+      }
+    }
+    __syncthreads();  // scratch and s_flag are reused by the next unit
+  }
+}
+
+// a4: h[b, :] = dequantize(embed[tokens[b]]) -- same arithmetic as dequantize_kernel (pie_misc.cu): one packed word
+// per thread, w_hat = bf16(bf16(q * scale) + bias).
+__device__ __noinline__ void embed_phase(const StepArgs& s, int bits) {
+  const int per = 32 / bits, wpr = s.hidden / per, gpr = s.hidden / kGroup;
+  const uint32_t mask = (1u << bits) - 1u;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < s.B * wpr; idx += gridDim.x * blockDim.x) {
+    const int b = idx / wpr, wi = idx % wpr;
+    int r = s.tokens[b];
+    r = r < 0 ? 0 : (r >= s.table_rows ? s.table_rows - 1 : r);
+    const uint32_t w = __ldg(s.e_wq + (size_t)r * wpr + wi);
+    const int grp = wi * per / kGroup;
+    const float sc = bf16lo((uint32_t)__ldg(s.e_s + (size_t)r * gpr + grp));
+    const float bi = bf16lo((uint32_t)__ldg(s.e_b + (size_t)r * gpr + grp));
+    uint16_t o[8];
+    for (int e = 0; e < per; ++e) o[e] = f2bf(bfround((float)((w >> (e * bits)) & mask) * sc) + bi);
+    uint16_t* dst = s.h + (size_t)b * s.hidden + (size_t)wi * per;
+    if (per == 8) *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(o);
+    else *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(o);
+  }
+}
+
+// greedy sampler + cache.offset += 1 (argmax_kernel, pie_misc.cu): first maximum; CTA b takes batch row b.
+__device__ __noinline__ void argmax_phase(const StepArgs& s, float* sv, int* si) {
+  for (int b = blockIdx.x; b < s.B; b += gridDim.x) {
+    const uint16_t* row = s.logits + (size_t)b * s.vocab;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < s.vocab; i += blockDim.x) {
+      const float v = bf16lo((uint32_t)ldcg16(row + i));
+      if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      const int nw = blockDim.x >> 5;
+      best = threadIdx.x < nw ? sv[threadIdx.x] : -INFINITY;
+      bi = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+      }
+      if (threadIdx.x == 0) {
+        const int tok = bi == 0x7fffffff ? 0 : bi;
+        s.tokens[b] = tok;
+        const int np = s.pos[b] + 1;
+        s.pos[b] = np;
+        if (s.seq && np < s.seq_ld) s.seq[(size_t)b * s.seq_ld + np] = tok;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Stand-alone form of the attention phase: one CTA per unit (pie_decode_attn_fused).
+template <int D, int R>
+__global__ void __launch_bounds__(kStepWarps * 32, 1) attn_fused_kernel(const __grid_constant__ StepArgs s,
+                                                                       const __grid_constant__ StepPhase P) {
+  __shared__ float scratch[kStepWarps * R * (D + 2)];
+  __shared__ int s_flag;
+  pdl_launch_dependents();
+  pdl_wait();
+  attn_phase<D, R>(s, P, scratch, &s_flag);
+}
+
+// The main loop of one matrix of the step.  Not inlined and free of calls: it needs the whole register file.
+template <int BITS, bool ONECOL>
+__device__ __noinline__ void step_matrix(const QmvArgs& a, uint8_t* smem, bool reinit) {
+  qmv_body<BITS, 1, ONECOL, true, QMV_MAIN>(a, smem, reinit, [] {});
+}
+
+template <int BITS, bool ONECOL>
+__global__ void __launch_bounds__(kStepWarps * 32, 1) decode_step_kernel(const __grid_constant__ StepArgs s) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ __align__(16) StepPhase ph[2];
+  __shared__ int s_flag;
+  static_assert(sizeof(StepPhase) % 4 == 0, "phase descriptors are copied word-wise");
+  constexpr int PHW = sizeof(StepPhase) / 4;
+  float* scratch = reinterpret_cast<float*>(smem + kQmvBarBytes +
+                                            (size_t)kStepWarps * kQmvStages * QmvGeom<BITS>::STAGE_BYTES);
+  for (int i = threadIdx.x; i < PHW; i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&ph[0])[i] = __ldg(reinterpret_cast<const uint32_t*>(s.phases) + i);
+  __syncthreads();
+  const bool tracing = s.trace && blockIdx.x == 0 && threadIdx.x == 0;
+  if (tracing) s.trace[0] = globaltimer_ns();
+  for (int p = 0; p < s.nphases; ++p) {
+    const StepPhase& P = ph[p & 1];
+    // this warp's first ring stages of matrix p go in flight before anything else
+    qmv_body<BITS, 1, ONECOL, true, QMV_PREFETCH>(P.q, smem, false, [] {});
+    // produce the matrix's input (embedding / attention) and wait for the rest of the grid
+    if (P.pre == PRE_EMBED) {
+      embed_phase(s, BITS);
+    } else if (P.pre == PRE_ATTN) {
+      grid_barrier(s.bar);
+      if (s.D == 128) {
+        if (s.R == 2) attn_phase<128, 2>(s, P, scratch, &s_flag);
+        else attn_phase<128, 1>(s, P, scratch, &s_flag);
+      } else {
+        if (s.R == 2) attn_phase<64, 2>(s, P, scratch, &s_flag);
+        else attn_phase<64, 1>(s, P, scratch, &s_flag);
+      }
+    }
+    grid_barrier(s.bar);
+    if (tracing) s.trace[2 + 2 * p] = globaltimer_ns();
+    if (p + 1 < s.nphases)  // the slot's previous user (matrix p - 1) is behind every warp of this CTA
+      for (int i = threadIdx.x; i < PHW; i += blockDim.x)
+        reinterpret_cast<uint32_t*>(&ph[(p + 1) & 1])[i] = __ldg(reinterpret_cast<const uint32_t*>(s.phases + p + 1) + i);
+    step_matrix<BITS, ONECOL>(P.q, smem, p > 0);  // its x staging ends with a CTA barrier: publishes the descriptor
+    if (tracing) s.trace[3 + 2 * p] = globaltimer_ns();
+  }
+  grid_barrier(s.bar);
+  if (tracing) s.trace[1] = globaltimer_ns();
+  argmax_phase(s, scratch, reinterpret_cast<int*>(scratch + 32));
+}
+
+template <int BITS, bool ONECOL>
+static cudaError_t launch_step_t(const StepArgs& s, int grid, size_t smem, cudaStream_t st) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(decode_step_kernel<BITS, ONECOL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kQmvMaxSmem - 2048);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3(kStepWarps * 32, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;  // every CTA must be resident: the kernel has grid barriers
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, decode_step_kernel<BITS, ONECOL>, s);
+}
+
+}  // namespace pie
+
+using namespace pie;
+
+extern "C" {
+
+size_t pie_decode_step_plan_bytes(int n_layers) {
+  if (n_layers <= 0) return 0;
+  return sizeof(StepHeader) + (size_t)(4 * n_layers + 1) * sizeof(StepPhase);
+}
+
+int pie_decode_step_pick_splits(int B, int Hq, int Hkv, int max_context) {
+  if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return 1;
+  const int n_rep = Hq / Hkv;
+  const int R = n_rep % 2 == 0 ? 2 : 1;  // query heads per unit (see pie_decode_step_plan)
+  const int rows = B * Hkv * (n_rep / R);
+  int ns = num_sms() / rows;                 // one unit per CTA when the context allows it
+  const int cap = (max_context + 63) / 64;   // a unit covers >= 64 tokens (4 per warp) of the longest context
+  if (ns > cap) ns = cap;
+  if (ns > 64) ns = 64;
+  return ns < 1 ? 1 : ns;
+}
+
+size_t pie_decode_step_attn_ws_bytes(int B, int Hq, int D, int nsplit) {
+  return pie_decode_attn_workspace_bytes(B, Hq, D, nsplit);
+}
+
+int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, const pie_step_io* io, void* plan_host,
+                         size_t plan_bytes) {
+  if (!m || !layers || !io || !plan_host) return PIE_ENULL;
+  if (m->n_layers <= 0 || io->B <= 0 || io->B > 8) return PIE_EUNSUPPORTED;
+  if (m->group_size != 64 || (m->bits != 4 && m->bits != 8)) return PIE_EUNSUPPORTED;
+  if (m->D != 64 && m->D != 128) return PIE_EUNSUPPORTED;
+  if (m->Hq <= 0 || m->Hkv <= 0 || m->Hq % m->Hkv || m->hidden % 64 || m->ffn % 64) return PIE_EINVAL_SHAPE;
+  if (plan_bytes < pie_decode_step_plan_bytes(m->n_layers)) return PIE_EWORKSPACE;
+  if (!io->tokens || !io->positions || !io->h || !io->qkv || !io->attn || !io->act || !io->logits) return PIE_ENULL;
+  if (!m->rope_freqs || !m->final_norm || !m->embed.wq || !m->embed.scales || !m->embed.biases) return PIE_ENULL;
+  const int B = io->B, hid = m->hidden, qd = m->Hq * m->D, qkvd = (m->Hq + 2 * m->Hkv) * m->D;
+  const int nsplit = io->nsplit < 1 ? 1 : io->nsplit;
+  if (nsplit > 1 && (!io->attn_ws || io->attn_ws_bytes < pie_decode_attn_workspace_bytes(B, m->Hq, m->D, nsplit)))
+    return PIE_EWORKSPACE;
+  memset(plan_host, 0, plan_bytes);
+  StepHeader* H = reinterpret_cast<StepHeader*>(plan_host);
+  StepPhase* ph = reinterpret_cast<StepPhase*>(H + 1);
+  size_t smem = 0;
+  int np = 0;
+  auto add = [&](void* out, int out_ld, const void* x, int x_ld, int K, const pie_qmv_seg* segs, int nseg,
+                 const void* norm, int epi, const void* residual, int pre) -> int {
+    QmvPlan pl;
+    StepPhase& P = ph[np];
+    const int st = build_qmv_args(P.q, pl, out, out_ld, x, x_ld, 0, B, K, segs, nseg, m->group_size, m->bits, norm,
+                                  m->rms_eps, epi, residual, 0, io->qmv_ws, io->qmv_ws_bytes, kStepWarps);
+    if (st != PIE_OK) return st;
+    const size_t need = qmv_smem_bytes(B, pl.kslice, m->bits, kStepWarps, 1) + (size_t)kStepWarps * 32 * kQmvProdWords * 4;
+    if (need > smem) smem = need;
+    P.pre = pre;
+    ++np;
+    return PIE_OK;
+  };
+  for (int i = 0; i < m->n_layers; ++i) {
+    const pie_step_layer& L = layers[i];
+    if (!L.kcache || !L.vcache || !L.input_norm || !L.post_norm) return PIE_ENULL;
+    if (L.kv.tok_stride < m->D || L.kv.tok_stride % 8 || L.kv.head_stride % 8 || L.kv.batch_stride % 8)
+      return PIE_EINVAL_SHAPE;
+    if (L.kv.page_table && (L.kv.page_size <= 0 || L.kv.pt_stride <= 0)) return PIE_EINVAL_SHAPE;
+    const pie_qmv_seg qkv[3] = {L.q, L.k, L.v};
+    const pie_qmv_seg gu[2] = {L.gate, L.up};
+    if (L.q.N != qd || L.k.N != m->Hkv * m->D || L.v.N != m->Hkv * m->D || L.o.N != hid || L.down.N != hid ||
+        L.gate.N != m->ffn || L.up.N != m->ffn) return PIE_EINVAL_SHAPE;
+    int st = add(io->qkv, qkvd, io->h, hid, hid, qkv, 3, L.input_norm, PIE_EPI_STORE, nullptr,
+                 i == 0 ? PRE_EMBED : PRE_BARRIER);
+    if (st != PIE_OK) return st;
+    st = add(io->h, hid, io->attn, qd, qd, &L.o, 1, nullptr, PIE_EPI_RESADD, io->h, PRE_ATTN);
+    if (st != PIE_OK) return st;
+    StepPhase& A = ph[np - 1];
+    A.qkv = (const uint16_t*)io->qkv; A.attn_out = (uint16_t*)io->attn;
+    A.kc = (uint16_t*)L.kcache; A.vc = (uint16_t*)L.vcache;
+    A.kv.batch_stride = L.kv.batch_stride; A.kv.head_stride = L.kv.head_stride; A.kv.tok_stride = L.kv.tok_stride;
+    A.kv.page_table = L.kv.page_table; A.kv.pt_stride = L.kv.pt_stride; A.kv.page_size = L.kv.page_size;
+    st = add(io->act, m->ffn, io->h, hid, hid, gu, 2, L.post_norm, PIE_EPI_SILUMUL, nullptr, PRE_BARRIER);
+    if (st != PIE_OK) return st;
+    st = add(io->h, hid, io->act, m->ffn, m->ffn, &L.down, 1, nullptr, PIE_EPI_RESADD, io->h, PRE_BARRIER);
+    if (st != PIE_OK) return st;
+  }
+  if (m->head.N != m->vocab) return PIE_EINVAL_SHAPE;
+  int st = add(io->logits, m->vocab, io->h, hid, hid, &m->head, 1, m->final_norm, PIE_EPI_STORE, nullptr, PRE_BARRIER);
+  if (st != PIE_OK) return st;
+  const int n_rep = m->Hq / m->Hkv;
+  // two query heads per unit: with 512 threads per CTA (128 registers each) four heads' fp32 accumulators spill
+  const int R = n_rep % 2 == 0 ? 2 : 1;
+  // the attention phase borrows the shared memory behind the weight rings: 16 warps x R x (D + 2) floats
+  const size_t stage = m->bits == 4 ? QmvGeom<4>::STAGE_BYTES : QmvGeom<8>::STAGE_BYTES;
+  const size_t attn_need = kQmvBarBytes + (size_t)kStepWarps * kQmvStages * stage +
+                           (size_t)kStepWarps * R * (m->D + 2) * sizeof(float);
+  if (attn_need > smem) smem = attn_need;
+  if (smem > (size_t)kQmvMaxSmem - 2048) return PIE_EUNSUPPORTED;
+  H->magic = kStepMagic; H->bits = (uint32_t)m->bits; H->grid = (uint32_t)num_sms(); H->smem = (uint32_t)smem;
+  H->onecol = B == 1; H->nphases = (uint32_t)np; H->plan_bytes = (uint32_t)plan_bytes;
+  StepArgs& s = H->args;
+  s.nphases = np; s.B = B; s.Hq = m->Hq; s.Hkv = m->Hkv; s.D = m->D; s.R = R; s.rg = n_rep / R; s.nsplit = nsplit;
+  s.scale_log2e = m->attn_scale * 1.4426950408889634f;
+  s.freqs = m->rope_freqs; s.pos = io->positions;
+  const size_t cnt_bytes = (((size_t)B * m->Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
+  s.attn_cnt = reinterpret_cast<unsigned int*>(io->attn_ws);
+  s.attn_part = io->attn_ws ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(io->attn_ws) + cnt_bytes) : nullptr;
+  s.e_wq = m->embed.wq; s.e_s = (const uint16_t*)m->embed.scales; s.e_b = (const uint16_t*)m->embed.biases;
+  s.tokens = io->tokens; s.table_rows = m->embed.N; s.hidden = hid; s.h = (uint16_t*)io->h;
+  s.trace = io->trace;
+  s.logits = (const uint16_t*)io->logits; s.vocab = m->vocab; s.seq = io->seq; s.seq_ld = io->seq_ld;
+  return PIE_OK;
+}
+
+int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache, const pie_kv_layout* kv,
+                          const int32_t* positions, const float* freqs, int B, int Hq, int Hkv, int D, float scale,
+                          int nsplit, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
+  if (B == 0) return PIE_OK;
+  if (!out || !qkv || !kcache || !vcache || !kv || !positions || !freqs) return PIE_ENULL;
+  if (B < 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return PIE_EINVAL_SHAPE;
+  if (D != 64 && D != 128) return PIE_EUNSUPPORTED;
+  if (kv->tok_stride < D || kv->tok_stride % 8 || kv->head_stride % 8 || kv->batch_stride % 8) return PIE_EINVAL_SHAPE;
+  if (kv->page_table && (kv->page_size <= 0 || kv->pt_stride <= 0)) return PIE_EINVAL_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(kcache) | reinterpret_cast<uintptr_t>(vcache)) & 15)
+    return PIE_EALIGN;
+  if (nsplit <= 0) nsplit = 1;
+  if (nsplit > 1 && (!workspace || workspace_bytes < pie_decode_attn_workspace_bytes(B, Hq, D, nsplit)))
+    return PIE_EWORKSPACE;
+  const int n_rep = Hq / Hkv, R = n_rep % 2 == 0 ? 2 : 1;
+  StepArgs s;
+  memset(&s, 0, sizeof(s));
+  StepPhase P;
+  memset(&P, 0, sizeof(P));
+  s.B = B; s.Hq = Hq; s.Hkv = Hkv; s.D = D; s.R = R; s.rg = n_rep / R; s.nsplit = nsplit;
+  s.scale_log2e = scale * 1.4426950408889634f;
+  s.freqs = freqs; s.pos = const_cast<int32_t*>(positions);
+  const size_t cnt_bytes = (((size_t)B * Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
+  s.attn_cnt = reinterpret_cast<unsigned int*>(workspace);
+  s.attn_part = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + cnt_bytes) : nullptr;
+  P.qkv = (const uint16_t*)qkv; P.attn_out = (uint16_t*)out; P.kc = (uint16_t*)kcache; P.vc = (uint16_t*)vcache;
+  P.kv.batch_stride = kv->batch_stride; P.kv.head_stride = kv->head_stride; P.kv.tok_stride = kv->tok_stride;
+  P.kv.page_table = kv->page_table; P.kv.pt_stride = kv->pt_stride; P.kv.page_size = kv->page_size;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(B * Hkv * s.rg * nsplit), 1, 1);
+  cfg.blockDim = dim3(kStepWarps * 32, 1, 1);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  count_launch();
+  cudaError_t e;
+  if (D == 128) e = R == 2 ? cudaLaunchKernelEx(&cfg, attn_fused_kernel<128, 2>, s, P) : cudaLaunchKernelEx(&cfg, attn_fused_kernel<128, 1>, s, P);
+  else e = R == 2 ? cudaLaunchKernelEx(&cfg, attn_fused_kernel<64, 2>, s, P) : cudaLaunchKernelEx(&cfg, attn_fused_kernel<64, 1>, s, P);
+  return status_of(e);
+}
+
+int pie_decode_step(const void* plan_dev, const void* plan_host, size_t plan_bytes, void* sync_ws, void* stream) {
+  if (!plan_dev || !plan_host || !sync_ws) return PIE_ENULL;
+  const StepHeader* H = reinterpret_cast<const StepHeader*>(plan_host);
+  if (plan_bytes < sizeof(StepHeader) || H->magic != kStepMagic || H->plan_bytes > plan_bytes) return PIE_EINVAL_SHAPE;
+  StepArgs s = H->args;
+  s.phases = reinterpret_cast<const StepPhase*>(reinterpret_cast<const uint8_t*>(plan_dev) + sizeof(StepHeader));
+  s.bar = reinterpret_cast<unsigned int*>(sync_ws);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  if (H->bits == 4) e = H->onecol ? launch_step_t<4, true>(s, H->grid, H->smem, st) : launch_step_t<4, false>(s, H->grid, H->smem, st);
+  else e = H->onecol ? launch_step_t<8, true>(s, H->grid, H->smem, st) : launch_step_t<8, false>(s, H->grid, H->smem, st);
+  return status_of(e);
+}
+
+}  // extern "C"

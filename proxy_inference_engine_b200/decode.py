@@ -21,7 +21,7 @@ import ctypes as C
 import torch
 
 from . import _lib, ops
-from ._lib import EPI_RESADD, EPI_SILUMUL, EPI_STORE, KvLayout, QmvSeg
+from ._lib import EPI_RESADD, EPI_SILUMUL, EPI_STORE, KvLayout, QmvSeg, StepIO, StepLayer, StepModel
 from .cache import KVCache, PagedKVCache
 from .llama import Model
 from .ops import _p, _stream
@@ -37,7 +37,8 @@ def _segs(*linears):
 
 class DecodeEngine:
     def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
-                 use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2):
+                 use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2,
+                 fused: bool = False, trace: bool = False, attn_fused: bool = True):
         a = model.args
         self.model, self.args, self.B, self.max_context = model, a, batch, max_context
         self.pdl, self.use_graph = int(pdl), use_graph
@@ -80,7 +81,10 @@ class DecodeEngine:
         L = _lib.load()
         self.L = L
         self.nsplit = L.pie_decode_attn_pick_splits(B, self.Hq, self.Hkv, max_context)
-        nb = L.pie_decode_attn_workspace_bytes(B, self.Hq, self.D, self.nsplit)
+        # rope + KV append + flash-decode in one launch (pie_decode_attn_fused) unless asked for the three-operator form
+        self.attn_fused = attn_fused
+        self.nsplit_fused = L.pie_decode_step_pick_splits(B, self.Hq, self.Hkv, max_context)
+        nb = L.pie_decode_attn_workspace_bytes(B, self.Hq, self.D, max(self.nsplit, self.nsplit_fused))
         self.attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
         # per-layer segment tables (host structs must outlive the captured graph: keep references)
         self.seg_qkv, self.seg_o, self.seg_gu, self.seg_down = [], [], [], []
@@ -101,6 +105,49 @@ class DecodeEngine:
         self.qmv_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
         self.graph = None
         self.launches_per_step = 0
+        # fused=True: one cooperative launch per step (pie_decode_step), B <= 8.  Round-1 status: parity-green but
+        # slower than the per-operator launches, hence opt-in
+        self.fused = bool(fused)
+        self.trace = trace
+        if self.fused:
+            self._plan_fused()
+
+    def _plan_fused(self):
+        """Describe the step to pie_decode_step_plan (host only) and upload the plan once."""
+        a, m, L, B = self.args, self.model, self.L, self.B
+        if B > 8:
+            raise ValueError("the fused decode step serves B <= 8")
+
+        def seg(l):
+            return QmvSeg(l.weight.data_ptr(), l.scales.data_ptr(), l.biases.data_ptr(), l.weight.shape[0])
+
+        layers = (StepLayer * len(m.layers))()
+        for i, ly in enumerate(m.layers):
+            at, mlp, s = ly.self_attn, ly.mlp, layers[i]
+            s.q, s.k, s.v, s.o = seg(at.q_proj), seg(at.k_proj), seg(at.v_proj), seg(at.o_proj)
+            s.gate, s.up, s.down = seg(mlp.gate_proj), seg(mlp.up_proj), seg(mlp.down_proj)
+            s.input_norm = ly.input_layernorm.weight.data_ptr()
+            s.post_norm = ly.post_attention_layernorm.weight.data_ptr()
+            s.kcache, s.vcache, s.kv = self.kbuf[i].data_ptr(), self.vbuf[i].data_ptr(), self.lay[i]
+        at0 = m.layers[0].self_attn
+        head = m.model.embed_tokens if a.tie_word_embeddings else m.lm_head
+        sm = StepModel(len(m.layers), a.hidden_size, a.intermediate_size, self.Hq, self.Hkv, self.D, a.vocab_size,
+                       self.bits, self.gs, float(a.rms_norm_eps), float(at0.scale), at0.rope._freqs.data_ptr(),
+                       seg(m.model.embed_tokens), seg(head), m.model.norm.weight.data_ptr())
+        self.step_nsplit = L.pie_decode_step_pick_splits(B, self.Hq, self.Hkv, self.max_context)
+        nb = L.pie_decode_step_attn_ws_bytes(B, self.Hq, self.D, self.step_nsplit)
+        self.step_attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=self.dev)
+        self.step_sync = torch.zeros(256, dtype=torch.uint8, device=self.dev)
+        self.step_trace = (torch.zeros(4 + 2 * (4 * len(m.layers) + 1), dtype=torch.int64, device=self.dev)
+                           if self.trace else None)
+        io = StepIO(B, _p(self.tokens), _p(self.positions), _p(self.seq), self.seq.shape[1], _p(self.h), _p(self.qkv),
+                    _p(self.attn), _p(self.act), _p(self.logits), _p(self.step_attn_ws), self.step_attn_ws.numel(),
+                    self.step_nsplit, _p(self.qmv_ws), self.qmv_ws.numel(), _p(self.step_trace))
+        nbytes = L.pie_decode_step_plan_bytes(len(m.layers))
+        self.plan_host = (C.c_uint8 * nbytes)()
+        _lib.check(L.pie_decode_step_plan(C.byref(sm), layers, C.byref(io), self.plan_host, nbytes), "decode_step_plan")
+        self.plan_dev = torch.frombuffer(self.plan_host, dtype=torch.uint8).clone().to(self.dev)
+        self._plan_keep = (layers, sm, io)
 
     # ------------------------------------------------------------------------------------------------
     def _qmv(self, out, out_ld, x, x_ld, K, segs, nseg, norm_w, epi, residual):
@@ -111,6 +158,10 @@ class DecodeEngine:
     def _step_kernels(self):
         """Enqueue one decode step on the current stream (capturable: no sync, no allocation)."""
         a, m, L = self.args, self.model, self.L
+        if self.fused:
+            _lib.check(L.pie_decode_step(_p(self.plan_dev), self.plan_host, len(self.plan_host), _p(self.step_sync),
+                                         _stream()), "decode_step")
+            return
         emb = m.model.embed_tokens
         h, hid = self.h, a.hidden_size
         _lib.check(L.pie_dequantize(_p(h), _p(emb.weight), _p(emb.scales), _p(emb.biases), _p(self.tokens), self.B,
@@ -122,11 +173,17 @@ class DecodeEngine:
             if "qkv" not in skip:
                 self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
                           EPI_STORE, None)
-            if "rope" not in skip:
+            if "attn" not in skip and self.attn_fused:
+                _lib.check(L.pie_decode_attn_fused(_p(self.attn), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
+                                                   C.byref(self.lay[i]), _p(self.positions),
+                                                   _p(ly.self_attn.rope._freqs), self.B, self.Hq, self.Hkv, self.D,
+                                                   float(ly.self_attn.scale), self.nsplit_fused, _p(self.attn_ws),
+                                                   self.attn_ws.numel(), self.pdl, _stream()), "decode_attn_fused")
+            if "rope" not in skip and not self.attn_fused:
                 _lib.check(L.pie_rope_kv_append(_p(self.q), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                             C.byref(self.lay[i]), _p(self.positions), _p(ly.self_attn.rope._freqs),
                                                 self.B, self.Hq, self.Hkv, self.D, _stream()), "rope_kv_append")
-            if "attn" not in skip:
+            if "attn" not in skip and not self.attn_fused:
                 _lib.check(L.pie_decode_attn(_p(self.attn), _p(self.q), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                          C.byref(self.lay[i]), _p(self.positions), self.B, self.Hq, self.Hkv, self.D,
                                          float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),

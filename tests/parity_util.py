@@ -56,7 +56,8 @@ def make_oracle(args, weights, mode="B"):
     return orc.LlamaOracle(oargs, weights_to_oracle(weights), mode=mode)
 
 
-def run_decode_parity(args, prompt_len=16, steps=8, batch=1, seed=0, paged=False, use_graph=True, pdl=True):
+def run_decode_parity(args, prompt_len=16, steps=8, batch=1, seed=0, paged=False, use_graph=True, pdl=True,
+                      fused=False):
     from proxy_inference_engine_b200.checkpoint import build_model, random_weights
     from proxy_inference_engine_b200.decode import DecodeEngine
 
@@ -65,7 +66,7 @@ def run_decode_parity(args, prompt_len=16, steps=8, batch=1, seed=0, paged=False
     o = make_oracle(args, w)
     prompt = torch.randint(0, args.vocab_size, (batch, prompt_len), generator=torch.Generator().manual_seed(1))
     eng = DecodeEngine(model, batch=batch, max_context=prompt_len + steps + 2, paged=paged, use_graph=use_graph,
-                       pdl=pdl)
+                       pdl=pdl, fused=fused)
     eng.prefill(prompt)
     caches = o.make_cache()
     lo = o(prompt.numpy(), caches, last_only=True)[:, -1]

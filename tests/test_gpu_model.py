@@ -34,6 +34,7 @@ def test_model_forward_matches_oracle_per_layer():
     assert cache[0].offset == 13
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("bits,tie,head_dim,batch,paged,graph", [
     (4, False, 64, 1, False, True),
     (8, False, 64, 1, False, True),
@@ -41,13 +42,47 @@ def test_model_forward_matches_oracle_per_layer():
     (8, False, 128, 3, True, True),
     (4, False, 64, 1, False, False),
 ])
-def test_decode_engine_parity(bits, tie, head_dim, batch, paged, graph):
+def test_decode_engine_parity(bits, tie, head_dim, batch, paged, graph, fused):
+    """fused=False: one launch per operator; fused=True: the whole step in one cooperative launch (pie_decode_step)."""
     args = tiny_args(bits=bits, tie=tie, head_dim=head_dim)
-    rep = run_decode_parity(args, prompt_len=20, steps=12, batch=batch, paged=paged, use_graph=graph)
+    rep = run_decode_parity(args, prompt_len=20, steps=12, batch=batch, paged=paged, use_graph=graph, fused=fused)
     assert rep["max_rel_err"] < TOL, rep
     assert rep["strong_mismatch"] == 0, rep
     assert rep["token_match"] >= 0.9, rep
-    assert rep["launches_per_step"] == 1 + 6 * args.num_hidden_layers + 2
+    assert rep["launches_per_step"] == (1 if fused else 1 + 5 * args.num_hidden_layers + 2)
+
+
+@pytest.mark.parametrize("bits,head_dim,batch,heads,kv_heads,ctx", [
+    (4, 128, 1, 8, 2, 40),      # n_rep 4 (the 8B / 1B grouping)
+    (4, 128, 2, 8, 1, 300),     # n_rep 8 (the 70B grouping): two query-head groups per kv head, several splits
+    (8, 64, 8, 4, 4, 150),      # n_rep 1, full batch of the fused step
+    (4, 64, 5, 8, 4, 700),      # n_rep 2, long context: several rounds per warp
+])
+def test_fused_step_matches_per_operator_path(bits, head_dim, batch, heads, kv_heads, ctx):
+    """pie_decode_step against the per-operator launches on the same engine state: same tokens, logits equal up to
+    the split-K merge order of attention (the GEMVs are the same code and bit-identical)."""
+    from proxy_inference_engine_b200.checkpoint import build_model, random_weights
+    from proxy_inference_engine_b200.decode import DecodeEngine
+    args = tiny_args(bits=bits, head_dim=head_dim, num_attention_heads=heads, num_key_value_heads=kv_heads,
+                     hidden_size=heads * head_dim if heads * head_dim >= 256 else 256)
+    model = build_model(args, random_weights(args, seed=7, device="cuda", gen_device="cpu"))
+    prompt = torch.randint(0, args.vocab_size, (batch, ctx), generator=torch.Generator().manual_seed(11))
+    outs = []
+    for fused, attn_fused in ((False, False), (True, True), (False, True)):
+        eng = DecodeEngine(model, batch, ctx + 40, fused=fused, attn_fused=attn_fused)
+        eng.prefill(prompt)
+        lg = []
+        for _ in range(6):
+            eng.step(1)
+            lg.append(eng.logits.float().clone())
+        outs.append((eng.generated(), torch.stack(lg), eng.cache))
+    (ta, la, ca), (tb, lb, cb), (tc, lc, cc) = outs   # three-operator attention / one launch per step / fused attention
+    assert rel_l2(lc.cpu().numpy(), la.cpu().numpy()) < 1e-2 and torch.equal(ta, tc)
+    assert rel_l2(lb.cpu().numpy(), la.cpu().numpy()) < 1e-2   # bf16 ulp is 4e-3: a few logits round differently
+    assert torch.equal(ta, tb)
+    n = ctx + 5
+    assert torch.equal(ca[-1].keys[:, :, :n], cb[-1].keys[:, :, :n]) or \
+        rel_l2(cb[-1].keys[:, :, :n].float().cpu().numpy(), ca[-1].keys[:, :, :n].float().cpu().numpy()) < 2e-3
 
 
 def test_decode_engine_is_deterministic_and_free_running():
