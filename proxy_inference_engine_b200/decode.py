@@ -19,6 +19,7 @@ from __future__ import annotations
 import ctypes as C
 
 import torch
+import torch.distributed as dist
 
 from . import _lib, ops
 from ._lib import EPI_RESADD, EPI_SILUMUL, EPI_STORE, KvLayout, QmvSeg, StepIO, StepLayer, StepModel
@@ -38,7 +39,7 @@ def _segs(*linears):
 class DecodeEngine:
     def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
                  use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2,
-                 fused: bool = False, trace: bool = False, attn_fused: bool = True):
+                 fused: bool = False, trace: bool = False, attn_fused: bool = True, tp=None):
         a = model.args
         self.model, self.args, self.B, self.max_context = model, a, batch, max_context
         self.pdl, self.use_graph = int(pdl), use_graph
@@ -58,6 +59,15 @@ class DecodeEngine:
         self.attn = torch.empty((B, self.Hq * self.D), dtype=bf, device=dev)
         self.act = torch.empty((B, a.intermediate_size), dtype=bf, device=dev)
         self.logits = torch.empty((B, a.vocab_size), dtype=bf, device=dev)
+        # tensor parallel (tp.py): this rank owns Hq/W query heads, Hkv/W kv heads, ffn/W columns and V/W logits
+        self.tp = tp if tp is not None else getattr(model, "tp", None)
+        self.tp_on = self.tp is not None and self.tp.on
+        if self.tp_on:
+            if fused:
+                raise ValueError("the one-launch decode step is single-GPU; tensor parallel uses the per-operator path")
+            w = self.tp.world
+            self.logits_local = torch.empty((B, a.vocab_size // w), dtype=bf, device=dev)
+            self.logits_gather = torch.empty((w * B, a.vocab_size // w), dtype=bf, device=dev)  # rank-major rows
         # caches
         self.paged = paged
         if paged:
@@ -96,11 +106,14 @@ class DecodeEngine:
             self.seg_o.append(_segs(at.o_proj))
             self.seg_gu.append(_segs(mlp.gate_proj, mlp.up_proj))
             self.seg_down.append(_segs(mlp.down_proj))
-        head = model.model.embed_tokens if a.tie_word_embeddings else model.lm_head
-        self.seg_head = _segs(head)
+        hw, hs, hb = model.head_slices()
+        self._head_keep = (hw, hs, hb)
+        self.seg_head = (QmvSeg * 1)()
+        self.seg_head[0].wq, self.seg_head[0].scales, self.seg_head[0].biases = hw.data_ptr(), hs.data_ptr(), hb.data_ptr()
+        self.seg_head[0].N = hw.shape[0]
         qd = self.Hq * self.D
         for (n, k, dual) in (((self.Hq + 2 * self.Hkv) * self.D, h, 0), (h, qd, 0), (a.intermediate_size, h, 1),
-                             (h, a.intermediate_size, 0), (a.vocab_size, h, 0)):
+                             (h, a.intermediate_size, 0), (hw.shape[0], h, 0)):
             nb = max(nb, L.pie_qmv_workspace_bytes(mb, n, k, self.bits, dual, 0))
         self.qmv_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
         self.graph = None
@@ -155,6 +168,18 @@ class DecodeEngine:
                                         _p(norm_w), float(self.args.rms_norm_eps), epi, _p(residual), 0,
                                         _p(self.qmv_ws), self.qmv_ws.numel(), self.pdl, _stream()), "qmv_fused")
 
+    def _qmv_rowsplit(self, h, hid, x, K, segs):
+        """h += x @ W^T for a matrix split by input columns (o_proj, down_proj).  Single GPU: residual-add epilogue.
+        Tensor parallel: rank 0 folds the residual into its partial sum, the others store theirs, and ONE all-reduce
+        over [B, hidden] leaves the new residual stream on every rank (the exchange step of
+        QuantizedShardedToAllLinear, MLX/python/mlx/nn/layers/distributed.py:459-566)."""
+        if not self.tp_on or self.tp.rank == 0:
+            self._qmv(h, hid, x, K, K, segs, 1, None, EPI_RESADD, h)
+        else:
+            self._qmv(h, hid, x, K, K, segs, 1, None, EPI_STORE, None)
+        if self.tp_on:
+            dist.all_reduce(h, op=dist.ReduceOp.SUM, group=self.tp.group)
+
     def _step_kernels(self):
         """Enqueue one decode step on the current stream (capturable: no sync, no allocation)."""
         a, m, L = self.args, self.model, self.L
@@ -189,14 +214,20 @@ class DecodeEngine:
                                          float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),
                                          self.attn_ws.numel(), _stream()), "decode_attn")
             if "o" not in skip:
-                self._qmv(h, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_RESADD, h)
+                self._qmv_rowsplit(h, hid, self.attn, qd, self.seg_o[i])
             if "gu" not in skip:
                 self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2,
                           ly.post_attention_layernorm.weight, EPI_SILUMUL, None)
             if "down" not in skip:
-                self._qmv(h, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None,
-                          EPI_RESADD, h)
-        self._qmv(self.logits, a.vocab_size, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+                self._qmv_rowsplit(h, hid, self.act, a.intermediate_size, self.seg_down[i])
+        if self.tp_on:
+            nl = self.logits_local.shape[1]
+            self._qmv(self.logits_local, nl, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+            dist.all_gather_into_tensor(self.logits_gather, self.logits_local, group=self.tp.group)
+            self.logits.view(self.B, self.tp.world, nl).copy_(
+                self.logits_gather.view(self.tp.world, self.B, nl).permute(1, 0, 2))
+        else:
+            self._qmv(self.logits, a.vocab_size, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
         _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
                                 _p(self.seq), self.seq.shape[1], _stream()), "argmax")
 

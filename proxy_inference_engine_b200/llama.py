@@ -13,6 +13,7 @@ import torch
 
 from . import nn, ops
 from .cache import KVCache, PagedKVCache
+from .tp import TPInfo, all_gather_last, all_reduce_sum
 
 
 @dataclass
@@ -33,6 +34,7 @@ class ModelArgs:
     tie_word_embeddings: bool = True
     model_type: str = "llama"
     quantization: dict = field(default_factory=lambda: {"group_size": 64, "bits": 4})
+    lm_head_rows: int | None = None  # tensor parallel: vocabulary rows of the head this rank owns (tp.shard_args)
 
     @classmethod
     def from_dict(cls, params: dict):
@@ -124,7 +126,8 @@ class Attention(nn.Module):
             queries, keys = self.rope(queries), self.rope(keys)
         output = scaled_dot_product_attention(queries, keys, values, cache=cache, scale=self.scale, mask=mask)
         output = output.transpose(1, 2).reshape(B, L, -1)
-        return self.o_proj(output)
+        # tensor parallel: o_proj holds a K slice; the ranks' partial sums meet in one all-reduce (tp.py)
+        return all_reduce_sum(self.o_proj(output), getattr(self, "tp", None))
 
 
 class MLP(nn.Module):
@@ -136,7 +139,7 @@ class MLP(nn.Module):
         self.up_proj = mk(args.hidden_size, args.intermediate_size)
 
     def __call__(self, x):
-        return self.down_proj(ops.silu_mul(self.gate_proj(x), self.up_proj(x)))
+        return all_reduce_sum(self.down_proj(ops.silu_mul(self.gate_proj(x), self.up_proj(x))), getattr(self, "tp", None))
 
 
 class TransformerBlock(nn.Module):
@@ -178,14 +181,36 @@ class Model(nn.Module):
         self.model = LlamaModel(args, device)
         if not args.tie_word_embeddings:
             q = args.quantization
-            self.lm_head = nn.QuantizedLinear(args.hidden_size, args.vocab_size, bias=False, group_size=q["group_size"],
-                                              bits=q["bits"], device=device)
+            self.lm_head = nn.QuantizedLinear(args.hidden_size, args.lm_head_rows or args.vocab_size, bias=False,
+                                              group_size=q["group_size"], bits=q["bits"], device=device)
+
+    def set_tp(self, tp: TPInfo):
+        """Mark this model as rank ``tp.rank`` of a tensor-parallel group (weights already sharded by tp.shard_weights)."""
+        self.tp = tp
+        for ly in self.model.layers:
+            ly.self_attn.tp = tp
+            ly.mlp.tp = tp
+        return self
+
+    def head_slices(self):
+        """(weight, scales, biases) of the output head this rank applies: lm_head, or -- tied -- the embedding rows
+        of this rank's vocabulary shard (QuantizedEmbedding.as_linear, quantized.py:109-124)."""
+        if not self.args.tie_word_embeddings:
+            return self.lm_head.weight, self.lm_head.scales, self.lm_head.biases
+        e = self.model.embed_tokens
+        tp = getattr(self, "tp", None)
+        if tp is None or not tp.on:
+            return e.weight, e.scales, e.biases
+        n = self.args.vocab_size // tp.world
+        lo, hi = tp.rank * n, (tp.rank + 1) * n
+        return e.weight[lo:hi], e.scales[lo:hi], e.biases[lo:hi]
 
     def __call__(self, inputs, mask=None, cache=None):
         out = self.model(inputs, mask, cache)
-        if self.args.tie_word_embeddings:
-            return self.model.embed_tokens.as_linear(out)
-        return self.lm_head(out)
+        q = self.args.quantization
+        w, s, b = self.head_slices()
+        logits = ops.quantized_matmul(out, w, s, b, transpose=True, group_size=q["group_size"], bits=q["bits"])
+        return all_gather_last(logits, getattr(self, "tp", None))
 
     def sanitize(self, weights: dict) -> dict:
         """language.py:212-219."""
