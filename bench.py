@@ -204,8 +204,14 @@ def run_b200(a):
     over = {"num_hidden_layers": a.layers} if a.layers else {}
     margs = preset_args(a.model, bits=a.bits, **over)
     torch.manual_seed(0)
-    weights = random_weights(margs, seed=0, device="cuda")
-    model = build_model(margs, weights)
+    if world > 1:
+        # tensor parallel over the box (tp.py): same model, sharded by heads / ffn columns / vocabulary rows
+        from proxy_inference_engine_b200 import tp as T
+        weights = random_weights(margs, seed=0, device="cuda", shard=(rank, world))
+        model = build_model(T.shard_args(margs, world), weights).set_tp(T.TPInfo(rank, world))
+    else:
+        weights = random_weights(margs, seed=0, device="cuda")
+        model = build_model(margs, weights)
     del weights
     B = a.batch
     max_ctx = a.prompt + a.warmup + a.steps * 2 + 64
@@ -249,37 +255,40 @@ def run_b200(a):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = float(t[0]), float(t[1])
+    # every rank takes part: the eager pass contains the tensor-parallel collectives
+    qsec, nlaunch = (0.0, 0) if a.no_kernel_timing else time_qmv_launches(eng)
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world)
         return
     nums = model_numbers(margs, a.bits)
     ctx_mid = ctx0 + a.steps / 2
     step_bytes = nums["weight_bytes"] + B * (ctx_mid * nums["kv_bytes_per_ctx_token"] + nums["embed_row_bytes"])
     peak, peak_src = measured_peaks()
-    value = world * B * a.steps / (ms * 1e-3)
+    value = B * a.steps / (ms * 1e-3)   # one model instance, whatever the GPU count (tensor parallel)
     line = {
         "metric": "decode tok/s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": a.steps,
         "warmup": max(a.warmup, 3), "ms_per_step": round(ms / a.steps, 5), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16 activations / fp32 accumulate over u4 weights"
+        "scaling": "weak" if world == 1 else "strong", "vs_baseline": None,
+        "dtype": "bf16 activations / fp32 accumulate over u4 weights"
         if a.bits == 4 else "bf16 activations / fp32 accumulate over u8 weights", "data": "synthetic",
         "config": {"workload": f"{a.model} random-init MLX q{a.bits} gs64, bs{B} greedy decode, prompt {a.prompt}, "
                                f"context {ctx0}..{ctx0 + a.steps}" + (", paged KV" if a.paged else ""),
-                   "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (TP not built yet)",
+                   "parallelism": "single GPU" if world == 1 else
+                   f"tp{world}: heads / ffn / vocab sharded, 2 NCCL all-reduces per layer + 1 all-gather of logits",
                    "l2": "each step streams the whole weight set (>> 126 MB L2), no flush needed",
                    "layers": margs.num_hidden_layers},
-        "e2e": {"value": round(world * B * a.steps / (e2e_ms * 1e-3), 2), "unit": "tok/s",
+        "e2e": {"value": round(B * a.steps / (e2e_ms * 1e-3), 2), "unit": "tok/s",
                 "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B},
         "gpu_launches": eng.launches_per_step * a.steps,
         "clocks": clocks,
-        "step_roofline": {"bytes_per_step": int(step_bytes), "achieved_GBps": round(step_bytes / (ms / a.steps) / 1e6, 1),
-                          "frac": round(step_bytes / (ms / a.steps) / 1e6 / peak, 4)},
+        "step_roofline": {"bytes_per_step_per_gpu": int(step_bytes / world),
+                          "achieved_GBps_per_gpu": round(step_bytes / world / (ms / a.steps) / 1e6, 1),
+                          "frac": round(step_bytes / world / (ms / a.steps) / 1e6 / peak, 4)},
     }
     if a.layers:
         line["invalid"] = "layer count overridden (debug run)"
     if not a.no_kernel_timing:
-        qsec, nlaunch = time_qmv_launches(eng)
-        qbytes = nums["weight_bytes"]  # every qmv launch of a step together reads the weight set once
+        qbytes = nums["weight_bytes"] / world  # the qmv launches of a step together read this GPU's weights once
         ach = qbytes / qsec / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}>", "achieved": round(ach, 1), "peak": peak,
                             "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
@@ -289,8 +298,18 @@ def run_b200(a):
     if not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(margs, a.bits)
     print(json.dumps(line), flush=True)
+    _finish(world)
+
+
+def _finish(world):
+    """Multi-rank exit: NCCL teardown after CUDA-graph capture of collectives can block; leave without it."""
     if world > 1:
-        dist.destroy_process_group()
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        os._exit(0)
 
 
 def run_reference(a):

@@ -57,10 +57,15 @@ def _linear_names(args: ModelArgs):
         yield "lm_head", args.vocab_size, h
 
 
-def random_weights(args: ModelArgs, seed: int = 0, device="cuda", gen_device=None, head_gain: float = 1.0) -> dict:
+def random_weights(args: ModelArgs, seed: int = 0, device="cuda", gen_device=None, head_gain: float = 1.0,
+                   shard: tuple | None = None) -> dict:
     """Random-init checkpoint in the MLX schema.  Linear: U(-1/sqrt(K), 1/sqrt(K)) (MLX nn/layers/linear.py:51-56);
     embedding: N(0, 1/sqrt(h)) (embedding.py:25); norm weights 1 + 0.1 N(0,1) so the weight multiply is exercised.
-    ``gen_device='cpu'`` makes the values independent of the GPU (the parity fixtures use it)."""
+    ``gen_device='cpu'`` makes the values independent of the GPU (the parity fixtures use it).
+    ``shard=(rank, world)``: every rank draws the same full tensors (same seed) and keeps only its tensor-parallel
+    slice (tp.shard_tensor), so a 70B model never has to sit whole on one GPU."""
+    from .tp import shard_tensor
+    rk, wd = shard if shard else (0, 1)
     gen_device = gen_device or device
     g = torch.Generator(device=gen_device).manual_seed(seed)
     gs, bits = args.quantization["group_size"], args.quantization["bits"]
@@ -68,7 +73,8 @@ def random_weights(args: ModelArgs, seed: int = 0, device="cuda", gen_device=Non
 
     def put_quant(name, t):
         wq, s, b = ops.quantize(t.to(torch.bfloat16).to(device), gs, bits)
-        w[name + ".weight"], w[name + ".scales"], w[name + ".biases"] = wq, s, b
+        for suffix, v in ((".weight", wq), (".scales", s), (".biases", b)):
+            w[name + suffix] = shard_tensor(name + suffix, v, rk, wd)
 
     h = args.hidden_size
     emb = torch.randn((args.vocab_size, h), generator=g, device=gen_device) * math.sqrt(1.0 / h)

@@ -14,6 +14,9 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 out = {}
+GRAPH = os.environ.get("TP_GRAPH", "1") == "1"
+def mark(m):
+    print(f"[rank {rank}] {m}", flush=True)
 for bits, tie in ((4, False), (8, True)):
     args = ModelArgs(hidden_size=1024, num_hidden_layers=3, intermediate_size=2048, num_attention_heads=8,
                      num_key_value_heads=world if world > 2 else 2, head_dim=128, vocab_size=1024, rms_norm_eps=1e-5,
@@ -25,12 +28,15 @@ for bits, tie in ((4, False), (8, True)):
     model = build_model(T.shard_args(args, world), T.shard_weights(full, args, rank, world)).set_tp(info)
     B, Lp, steps = 2, 24, 16
     prompt = torch.randint(0, args.vocab_size, (B, Lp), generator=torch.Generator().manual_seed(1))
-    eng = DecodeEngine(model, batch=B, max_context=Lp + steps + 8)
+    mark("model built")
+    eng = DecodeEngine(model, batch=B, max_context=Lp + steps + 8, use_graph=GRAPH)
     eng.prefill(prompt)
+    torch.cuda.synchronize(); mark("prefill done")
     lg = []
     for _ in range(steps):
         eng.step(1); lg.append(eng.logits.float().clone())
     toks = eng.generated()
+    mark("decode done")
     if rank == 0:
         ref_model = build_model(args, full)
         ref = DecodeEngine(ref_model, batch=B, max_context=Lp + steps + 8)
@@ -49,4 +55,4 @@ if rank == 0:
     print(json.dumps({"world": world, "results": out}))
     ok = all(v["rel_err"] < 2e-2 and v["tokens_equal_steps"] >= 8 for v in out.values())
     print("TP_CHECK", "PASS" if ok else "FAIL")
-dist.destroy_process_group()
+dist.barrier(); sys.stdout.flush(); os._exit(0)  # NCCL teardown after graph capture can block
