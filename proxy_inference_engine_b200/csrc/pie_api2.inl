@@ -14,10 +14,19 @@ static int check_kv(const pie_kv_layout* k, int D) {
 
 extern "C" {
 
-// Round-1 status: the same contraction as pie_qmv, run as passes of 8 activation rows (weights re-read per
-// pass).  The tcgen05/TMEM tile kernel replaces the body without changing this entry point.
+// M >= 64: the tcgen05 / TMEM tile kernel (pie_qmm.cu), weights dequantised once to bf16 into shared memory.
+// Smaller M, or shapes off its grid (K % 128, unaligned pointers): the decode GEMV in passes of <= 32 rows.
 int pie_qmm(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,
             int K, int group_size, int bits, void* workspace, size_t workspace_bytes, void* stream) {
+  if (M == 0 || N == 0) return PIE_OK;
+  if (!y || !x || !wq || !scales || !biases) return PIE_ENULL;
+  if (M < 0 || N < 0 || K <= 0) return PIE_EINVAL_SHAPE;
+  const bool tc = M >= 64 && quant_supported(group_size, bits) && K % 128 == 0 && aligned16(x) && aligned16(wq) &&
+                  aligned16(y) && !(reinterpret_cast<uintptr_t>(scales) & 3) &&
+                  !(reinterpret_cast<uintptr_t>(biases) & 3) && env_int("PIE_QMM_TC", 1) != 0;
+  if (tc)
+    return cuda_status(launch_qmm_tc((uint16_t*)y, (const uint16_t*)x, wq, (const uint16_t*)scales,
+                                     (const uint16_t*)biases, M, N, K, bits, (cudaStream_t)stream));
   return pie_qmv(y, x, wq, scales, biases, M, N, K, group_size, bits, workspace, workspace_bytes, stream);
 }
 

@@ -66,6 +66,8 @@ cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, int grid, bool pdl
 cudaError_t launch_qmv_generic(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s,
                                const uint16_t* b, int M, int N, int K, int gs, int bits, cudaStream_t st);
 size_t qmv_smem_bytes(int M, int kslice, int bits, int warps, int mt);
+cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s, const uint16_t* b,
+                          int M, int N, int K, int bits, cudaStream_t st);
 int qmv_mt(int M);
 int num_sms();
 

@@ -1,0 +1,260 @@
+// Prefill quantized GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
+//
+// Replaces mx.quantized_matmul(transpose=True) at prefill-sized M (MLX/mlx/ops.cpp:3984-4021; Metal qmm_t,
+// MLX/mlx/backend/metal/kernels/quantized.h:954-1078):  y[m, n] = bf16( sum_k x[m, k] * w_hat[n, k] ),
+// w_hat = bf16(scale * q + bias): the weight is dequantised ONCE to the activation type into shared memory
+// (QuantizedBlockLoader, quantized.h:411-417, 502-512) and the contraction accumulates in fp32 -- the same rounding
+// structure here, with the fp32 accumulator in tensor memory.
+//
+// One CTA computes a 256 x 128 tile of y (two 128-row accumulators, 256 TMEM columns).  Per 64-element K step
+// (= one quantization group) and pipeline stage:
+//   * warps 0-3 (128 threads, thread t <-> tile row t): cp.async the two 128 x 64 bf16 activation blocks into the
+//     128B-swizzled K-major layout tcgen05 reads; load weight row n0 + t (64 packed values + its scale / bias),
+//     dequantise in registers and store the row into the swizzled B block; fence.proxy.async; arrive on full[s].
+//   * warp 4, one elected lane: wait full[s]; 2 x 4 tcgen05.mma.kind::f16 (M128 N128 K16, bf16 x bf16 -> fp32) with
+//     shared-memory matrix descriptors; tcgen05.commit -> empty[s] hands the stage back to the producers.
+//   The dequantised weights of a stage serve both accumulators, so the ALU cost per MMA is half that of a 128 x 128
+//   tile; the activations (bf16, L2-resident across the CTAs of a row band) need no arithmetic.
+//   * epilogue: warps 0-3 read their TMEM lane quadrant with tcgen05.ld (32 lanes x 32 columns at a time), round to
+//     bf16 once and store.
+#include "pie_internal.h"
+#include "pie_ptx.cuh"
+
+namespace pie {
+
+constexpr int kQmmBM = 256, kQmmBN = 128, kQmmBK = 64, kQmmStages = 4;
+constexpr int kQmmAStage = kQmmBM * kQmmBK * 2;   // 32 KB
+constexpr int kQmmBStage = kQmmBN * kQmmBK * 2;   // 16 KB
+constexpr int kQmmSmem = kQmmStages * (kQmmAStage + kQmmBStage) + 1024;  // + alignment slack
+constexpr int kQmmTmemCols = 256;
+
+struct QmmArgs {
+  uint16_t* y;
+  const uint16_t* x;
+  const uint32_t* wq;
+  const uint16_t* scales;
+  const uint16_t* biases;
+  int M, N, K;
+};
+
+// shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);  // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                        // leading byte offset: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset between 8-row groups
+  d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, A = B = bf16, both K-major, M 128, N 128
+constexpr uint32_t kQmmIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kQmmBN >> 3) << 17) | ((128u >> 4) << 24);
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc),
+      "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+      "%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <int BITS>
+__global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ QmmArgs a) {
+  constexpr int S = kQmmStages, LAG = 2, RAW = LAG + 1;
+  constexpr int WPR = kQmmBK * BITS / 32;    // packed words of one row per K step: 8 (q4) / 16 (q8)
+  constexpr int RAW_BYTES = WPR * 4 + 16;    // + (scale pair, bias pair, pad)
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[S], empty_bar[S], accum_bar;
+  __shared__ uint32_t tmem_slot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smA = base, smB = base + S * kQmmAStage, smRaw = smB + S * kQmmBStage;
+  const int n0 = blockIdx.x * kQmmBN, m0 = blockIdx.y * kQmmBM;
+  const int nk = a.K / kQmmBK;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&accum_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) {  // one warp owns the tensor-memory allocation: 2 accumulators of 128 fp32 columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "n"(kQmmTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_slot;
+
+  if (warp < 4) {
+    // ---------------- producers: thread t <-> row t of the activation blocks and of the weight block ----------
+    const int t = tid;
+    const uint32_t swz = (uint32_t)(t & 7);
+    const int nrow = min(n0 + t, a.N - 1);
+    const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wq) + (size_t)nrow * (a.K * BITS / 8);
+    const uint16_t* ssrc = a.scales + (size_t)nrow * nk;
+    const uint16_t* bsrc = a.biases + (size_t)nrow * nk;
+    const uint16_t* xsrc0 = a.x + (size_t)min(m0 + t, a.M - 1) * a.K;
+    const uint16_t* xsrc1 = a.x + (size_t)min(m0 + 128 + t, a.M - 1) * a.K;
+    const uint32_t raw0 = smRaw + (uint32_t)t * (RAW * RAW_BYTES);
+    for (int kb = 0; kb < nk + LAG; ++kb) {
+      if (kb < nk) {
+        const int s = kb % S, it = kb / S;
+        if (it > 0) mbar_wait(&empty_bar[s], (uint32_t)(it - 1) & 1);
+        const uint32_t dA = smA + s * kQmmAStage + t * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          cp_async16(dA + ((c ^ swz) << 4), xsrc0 + kb * kQmmBK + c * 8);
+          cp_async16(dA + 128 * 128 + ((c ^ swz) << 4), xsrc1 + kb * kQmmBK + c * 8);
+        }
+        const uint32_t rw = raw0 + (kb % RAW) * RAW_BYTES;
+#pragma unroll
+        for (int c = 0; c < WPR / 4; ++c) cp_async16(rw + c * 16, wsrc + (size_t)kb * (WPR * 4) + c * 16);
+        cp_async4(rw + WPR * 4, ssrc + (kb & ~1));
+        cp_async4(rw + WPR * 4 + 4, bsrc + (kb & ~1));
+      }
+      cp_async_commit();
+      if (kb >= LAG) {
+        const int j = kb - LAG, s = j % S;
+        cp_async_wait<LAG>();  // this thread's copies of K step j have landed (its own raw words included)
+        const uint32_t rw = raw0 + (j % RAW) * RAW_BYTES;
+        const uint32_t sp = lds32(rw + WPR * 4), bp = lds32(rw + WPR * 4 + 4);
+        const float sc = j & 1 ? bf16hi(sp) : bf16lo(sp), bi = j & 1 ? bf16hi(bp) : bf16lo(bp);
+        const uint32_t dB = smB + s * kQmmBStage + t * 128;
+#pragma unroll
+        for (int c4 = 0; c4 < WPR / 4; ++c4) {
+          const uint4 wv = lds128(rw + c4 * 16);
+          const uint32_t w[4] = {wv.x, wv.y, wv.z, wv.w};
+          if (BITS == 4) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {  // word -> 8 values -> one 16-byte chunk
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float lo = fmaf((float)((w[i] >> (8 * e)) & 15u), sc, bi);
+                const float hi = fmaf((float)((w[i] >> (8 * e + 4)) & 15u), sc, bi);
+                o[e] = pack_bf16(lo, hi);
+              }
+              const uint32_t c = (uint32_t)(c4 * 4 + i);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dB + ((c ^ swz) << 4)), "r"(o[0]), "r"(o[1]),
+                           "r"(o[2]), "r"(o[3]) : "memory");
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {  // two words -> 8 values -> one 16-byte chunk
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const uint32_t ww = w[2 * i + (e >> 1)];
+                const float lo = fmaf((float)((ww >> (16 * (e & 1))) & 255u), sc, bi);
+                const float hi = fmaf((float)((ww >> (16 * (e & 1) + 8)) & 255u), sc, bi);
+                o[e] = pack_bf16(lo, hi);
+              }
+              const uint32_t c = (uint32_t)(c4 * 2 + i);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dB + ((c ^ swz) << 4)), "r"(o[0]), "r"(o[1]),
+                           "r"(o[2]), "r"(o[3]) : "memory");
+            }
+          }
+        }
+        fence_proxy_async();  // generic-proxy writes (cp.async, st.shared) -> visible to the tensor core's async proxy
+        mbar_arrive(&full_bar[s]);
+      }
+    }
+    // ---------------- epilogue: TMEM lane quadrant `warp` -> bf16 rows of y ----------------------------------
+    mbar_wait(&accum_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+      const int row = m0 + h * 128 + warp * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < kQmmBN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tmem + (uint32_t)(h * 128 + c * 32) + ((uint32_t)(warp * 32) << 16), v);
+        const int col = n0 + c * 32;
+        if (row < a.M) {
+          uint16_t* dst = a.y + (size_t)row * a.N + col;
+          if (col + 32 <= a.N && (a.N & 7) == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack_bf16(__uint_as_float(v[8 * q]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              reinterpret_cast<uint4*>(dst)[q] = o;
+            }
+          } else {
+            for (int q = 0; q < 32; ++q)
+              if (col + q < a.N) dst[q] = f2bf(__uint_as_float(v[q]));
+          }
+        }
+      }
+    }
+  } else {
+    // ---------------- MMA issuer: one elected lane of warp 4 ------------------------------------------------
+    for (int kb = 0; kb < nk; ++kb) {
+      const int s = kb % S;
+      mbar_wait(&full_bar[s], (uint32_t)(kb / S) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (lane == 0) {
+        const uint64_t db0 = umma_desc_sw128(smB + s * kQmmBStage);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const uint64_t da0 = umma_desc_sw128(smA + s * kQmmAStage + h * 128 * 128);
+#pragma unroll
+          for (int k4 = 0; k4 < kQmmBK / 16; ++k4)  // 16 bf16 = 32 bytes along K inside the swizzle atom: +2 units
+            umma_bf16(tmem + h * 128, da0 + 2 * k4, db0 + 2 * k4, kQmmIdesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // arrives when the MMAs above have read the stage
+        if (kb == nk - 1) umma_commit(&accum_bar);
+      }
+      __syncwarp();
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 4)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kQmmTmemCols) : "memory");
+}
+
+cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s, const uint16_t* b,
+                          int M, int N, int K, int bits, cudaStream_t st) {
+  QmmArgs a;
+  a.y = y; a.x = x; a.wq = wq; a.scales = s; a.biases = b; a.M = M; a.N = N; a.K = K;
+  const int raw = 128 * 3 * ((kQmmBK * bits / 32) * 4 + 16);
+  const size_t smem = (size_t)kQmmSmem + raw;
+  static bool configured[2] = {false, false};
+  const int idx = bits == 4 ? 0 : 1;
+  if (!configured[idx]) {
+    cudaError_t e = bits == 4 ? cudaFuncSetAttribute(qmm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                              : cudaFuncSetAttribute(qmm_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured[idx] = true;
+  }
+  const dim3 grid((N + kQmmBN - 1) / kQmmBN, (M + kQmmBM - 1) / kQmmBM);
+  count_launch();
+  if (bits == 4) qmm_tc_kernel<4><<<grid, 160, smem, st>>>(a);
+  else qmm_tc_kernel<8><<<grid, 160, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace pie

@@ -76,6 +76,34 @@ def test_quantized_matmul(env, bits, M, N, K):
     assert rel_l2(got, dense) < 6e-3
 
 
+# prefill sizes: M >= 64 runs on the tcgen05 / TMEM tile kernel (pie_qmm.cu): ragged M and N tiles, one and many K steps
+QMM_TC_CASES = [(64, 128, 128), (128, 128, 256), (200, 384, 512), (256, 200, 1024), (300, 1024, 4096),
+                (1000, 264, 1152), (513, 4096, 2048), (96, 16, 14336)]
+
+
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("M,N,K", QMM_TC_CASES)
+def test_quantized_matmul_prefill_tensor_core(env, bits, M, N, K):
+    """Same contraction with the rounding structure of Metal qmm_t (kernels/quantized.h:954-1078): weights rounded once
+    to bf16, fp32 accumulate.  Checked against that exact structure in fp32 on the host and against the fp32-dequant
+    dense product of MLX's own test (test_quantized.py:119-169)."""
+    orc, ops = env
+    rng = np.random.default_rng(M + 3 * N + K + bits)
+    wq, s, b = orc.quantize(_rand_w(rng, N, K), 64, bits)
+    x = orc.round_bf16(rng.standard_normal((M, K)).astype(np.float32))
+    got = t2n(ops.quantized_matmul(n2t_bf16(x), n2t_words(wq), n2t_bf16(s), n2t_bf16(b), True, 64, bits))
+    assert got.shape == (M, N)
+    w32 = orc.dequantize(wq, s, b, 64, bits, t_bf16=False)
+    ref = orc.round_bf16(x.astype(np.float64) @ orc.round_bf16(w32).astype(np.float64).T)
+    assert rel_l2(got, ref) < 2e-3, rel_l2(got, ref)
+    assert np.all(np.abs(got - ref) <= np.abs(ref) * 2.0 ** -7 + 1e-3 * np.abs(ref).max())
+    assert rel_l2(got, x @ w32.T) < 6e-3
+    # and the decode GEMV on the same rows agrees within bf16 rounding of the weights
+    rows = n2t_bf16(x[:8])
+    small = t2n(ops.quantized_matmul(rows, n2t_words(wq), n2t_bf16(s), n2t_bf16(b), True, 64, bits))
+    assert rel_l2(got[:8], small) < 6e-3
+
+
 @pytest.mark.parametrize("gs,bits,K", [(32, 4, 96), (128, 8, 384), (64, 2, 192), (64, 4, 64)])
 def test_quantized_matmul_generic_path(env, gs, bits, K):
     orc, ops = env
