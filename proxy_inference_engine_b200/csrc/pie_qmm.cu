@@ -6,27 +6,30 @@
 // (QuantizedBlockLoader, quantized.h:411-417, 502-512) and the contraction accumulates in fp32 -- the same rounding
 // structure here, with the fp32 accumulator in tensor memory.
 //
-// One CTA computes a 256 x 128 tile of y (two 128-row accumulators, 256 TMEM columns).  Per 64-element K step
-// (= one quantization group) and pipeline stage:
-//   * warps 0-3 (128 threads, thread t <-> tile row t): cp.async the two 128 x 64 bf16 activation blocks into the
-//     128B-swizzled K-major layout tcgen05 reads; load weight row n0 + t (64 packed values + its scale / bias),
-//     dequantise in registers and store the row into the swizzled B block; fence.proxy.async; arrive on full[s].
-//   * warp 4, one elected lane: wait full[s]; 2 x 4 tcgen05.mma.kind::f16 (M128 N128 K16, bf16 x bf16 -> fp32) with
+// One CTA computes a 256 x 256 tile of y: two 128-row accumulators of 256 fp32 columns = all 512 TMEM columns.
+// Per 64-element K step (= one quantization group) and pipeline stage (3 stages of 32 KB A + 32 KB B):
+//   * warps 0-7 (256 threads, thread t <-> activation row t and weight row t of the tile): cp.async the activation
+//     row into the 128B-swizzled K-major layout tcgen05 reads; dequantise weight row n0 + t (64 packed values, its
+//     scale and bias prefetched into registers one K step ahead) and store it into the swizzled B block;
+//     fence.proxy.async; arrive on full[s] one iteration later, when the activation copies have landed.
+//   * warp 8, one elected lane: wait full[s]; 2 x 4 tcgen05.mma.kind::f16 (M128 N256 K16, bf16 x bf16 -> fp32) with
 //     shared-memory matrix descriptors; tcgen05.commit -> empty[s] hands the stage back to the producers.
-//   The dequantised weights of a stage serve both accumulators, so the ALU cost per MMA is half that of a 128 x 128
-//   tile; the activations (bf16, L2-resident across the CTAs of a row band) need no arithmetic.
-//   * epilogue: warps 0-3 read their TMEM lane quadrant with tcgen05.ld (32 lanes x 32 columns at a time), round to
-//     bf16 once and store.
+//   Tile shape: the bf16 activations are the heavy operand (the 4-bit weights are 1/4 of their bytes), so the tile
+//   is made wide in N: 256 x 256 needs 40 KB of L2->SM traffic per 8.4 MFLOP; 256 x 128 measured L2-bound.
+//   * epilogue: the 8 warps read (accumulator, TMEM lane quadrant) = (warp / 4, warp % 4) with tcgen05.ld, 32 lanes x
+//     32 columns at a time, round to bf16 once and store.
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
 
 namespace pie {
 
-constexpr int kQmmBM = 256, kQmmBN = 128, kQmmBK = 64, kQmmStages = 4;
+constexpr int kQmmBM = 256, kQmmBN = 256, kQmmBK = 64, kQmmStages = 3;
 constexpr int kQmmAStage = kQmmBM * kQmmBK * 2;   // 32 KB
-constexpr int kQmmBStage = kQmmBN * kQmmBK * 2;   // 16 KB
+constexpr int kQmmBStage = kQmmBN * kQmmBK * 2;   // 32 KB
 constexpr int kQmmSmem = kQmmStages * (kQmmAStage + kQmmBStage) + 1024;  // + alignment slack
-constexpr int kQmmTmemCols = 256;
+constexpr int kQmmTmemCols = 512;
+constexpr int kQmmProducers = 256;                   // 8 warps: two threads per tile row (latency hiding for the dequant)
+constexpr int kQmmThreads = kQmmProducers + 32;      // + the MMA warp
 
 struct QmmArgs {
   uint16_t* y;
@@ -47,7 +50,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, A = B = bf16, both K-major, M 128, N 128
+// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, A = B = bf16, both K-major, M 128, N 256
 constexpr uint32_t kQmmIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kQmmBN >> 3) << 17) | ((128u >> 4) << 24);
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
@@ -76,25 +79,24 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 }
 
 template <int BITS>
-__global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ QmmArgs a) {
-  constexpr int S = kQmmStages, LAG = 2, RAW = LAG + 1;
+__global__ void __launch_bounds__(kQmmThreads, 1) qmm_tc_kernel(const __grid_constant__ QmmArgs a) {
+  constexpr int S = kQmmStages, LAG = 1;
   constexpr int WPR = kQmmBK * BITS / 32;    // packed words of one row per K step: 8 (q4) / 16 (q8)
-  constexpr int RAW_BYTES = WPR * 4 + 16;    // + (scale pair, bias pair, pad)
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[S], empty_bar[S], accum_bar;
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t smA = base, smB = base + S * kQmmAStage, smRaw = smB + S * kQmmBStage;
+  const uint32_t smA = base, smB = base + S * kQmmAStage;
   const int n0 = blockIdx.x * kQmmBN, m0 = blockIdx.y * kQmmBM;
   const int nk = a.K / kQmmBK;
 
   if (tid == 0) {
-    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], 128); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < S; ++s) { mbar_init(&full_bar[s], kQmmProducers); mbar_init(&empty_bar[s], 1); }
     mbar_init(&accum_bar, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {  // one warp owns the tensor-memory allocation: 2 accumulators of 128 fp32 columns
+  if (warp == kQmmProducers / 32) {  // one warp owns the tensor-memory allocation: 2 accumulators of 256 fp32 columns
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
                  "n"(kQmmTmemCols)
                  : "memory");
@@ -105,45 +107,43 @@ __global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ 
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = tmem_slot;
 
-  if (warp < 4) {
-    // ---------------- producers: thread t <-> row t of the activation blocks and of the weight block ----------
+  if (warp < kQmmProducers / 32) {
+    // ---------------- producers: thread t <-> activation row t (of 256) and weight row t (of 256) --------------
     const int t = tid;
     const uint32_t swz = (uint32_t)(t & 7);
     const int nrow = min(n0 + t, a.N - 1);
-    const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.wq) + (size_t)nrow * (a.K * BITS / 8);
+    const uint4* wsrc = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(a.wq) +
+                                                       (size_t)nrow * (a.K * BITS / 8));
     const uint16_t* ssrc = a.scales + (size_t)nrow * nk;
     const uint16_t* bsrc = a.biases + (size_t)nrow * nk;
-    const uint16_t* xsrc0 = a.x + (size_t)min(m0 + t, a.M - 1) * a.K;
-    const uint16_t* xsrc1 = a.x + (size_t)min(m0 + 128 + t, a.M - 1) * a.K;
-    const uint32_t raw0 = smRaw + (uint32_t)t * (RAW * RAW_BYTES);
+    const uint16_t* xsrc = a.x + (size_t)min(m0 + t, a.M - 1) * a.K;
+    // packed words, scale and bias of the NEXT K step travel in registers: one whole iteration hides their latency
+    uint4 wn[WPR / 4];
+    uint32_t sn, bn;
+#pragma unroll
+    for (int c = 0; c < WPR / 4; ++c) wn[c] = __ldg(wsrc + c);
+    sn = __ldg(ssrc); bn = __ldg(bsrc);
     for (int kb = 0; kb < nk + LAG; ++kb) {
       if (kb < nk) {
         const int s = kb % S, it = kb / S;
         if (it > 0) mbar_wait(&empty_bar[s], (uint32_t)(it - 1) & 1);
         const uint32_t dA = smA + s * kQmmAStage + t * 128;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          cp_async16(dA + ((c ^ swz) << 4), xsrc0 + kb * kQmmBK + c * 8);
-          cp_async16(dA + 128 * 128 + ((c ^ swz) << 4), xsrc1 + kb * kQmmBK + c * 8);
-        }
-        const uint32_t rw = raw0 + (kb % RAW) * RAW_BYTES;
+        for (int c = 0; c < 8; ++c) cp_async16(dA + ((c ^ swz) << 4), xsrc + kb * kQmmBK + c * 8);
+        cp_async_commit();
+        uint4 wc[WPR / 4];
 #pragma unroll
-        for (int c = 0; c < WPR / 4; ++c) cp_async16(rw + c * 16, wsrc + (size_t)kb * (WPR * 4) + c * 16);
-        cp_async4(rw + WPR * 4, ssrc + (kb & ~1));
-        cp_async4(rw + WPR * 4 + 4, bsrc + (kb & ~1));
-      }
-      cp_async_commit();
-      if (kb >= LAG) {
-        const int j = kb - LAG, s = j % S;
-        cp_async_wait<LAG>();  // this thread's copies of K step j have landed (its own raw words included)
-        const uint32_t rw = raw0 + (j % RAW) * RAW_BYTES;
-        const uint32_t sp = lds32(rw + WPR * 4), bp = lds32(rw + WPR * 4 + 4);
-        const float sc = j & 1 ? bf16hi(sp) : bf16lo(sp), bi = j & 1 ? bf16hi(bp) : bf16lo(bp);
+        for (int c = 0; c < WPR / 4; ++c) wc[c] = wn[c];
+        const float sc = bf16lo(sn), bi = bf16lo(bn);
+        if (kb + 1 < nk) {
+#pragma unroll
+          for (int c = 0; c < WPR / 4; ++c) wn[c] = __ldg(wsrc + (size_t)(kb + 1) * (WPR / 4) + c);
+          sn = __ldg(ssrc + kb + 1); bn = __ldg(bsrc + kb + 1);
+        }
         const uint32_t dB = smB + s * kQmmBStage + t * 128;
 #pragma unroll
         for (int c4 = 0; c4 < WPR / 4; ++c4) {
-          const uint4 wv = lds128(rw + c4 * 16);
-          const uint32_t w[4] = {wv.x, wv.y, wv.z, wv.w};
+          const uint32_t w[4] = {wc[c4].x, wc[c4].y, wc[c4].z, wc[c4].w};
           if (BITS == 4) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {  // word -> 8 values -> one 16-byte chunk
@@ -175,20 +175,26 @@ __global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ 
             }
           }
         }
-        fence_proxy_async();  // generic-proxy writes (cp.async, st.shared) -> visible to the tensor core's async proxy
-        mbar_arrive(&full_bar[s]);
+      } else {
+        cp_async_commit();
+      }
+      if (kb >= LAG) {
+        const int j = kb - LAG;
+        cp_async_wait<LAG>();  // this thread's activation copies of K step j have landed
+        fence_proxy_async();   // generic-proxy writes (cp.async, st.shared) -> visible to the tensor core's async proxy
+        mbar_arrive(&full_bar[j % S]);
       }
     }
     // ---------------- epilogue: TMEM lane quadrant `warp` -> bf16 rows of y ----------------------------------
     mbar_wait(&accum_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll 1
-    for (int h = 0; h < 2; ++h) {
-      const int row = m0 + h * 128 + warp * 32 + lane;
+    {
+      const int h = warp >> 2, quad = warp & 3;  // a warp reads TMEM lanes 32 (warp % 4) .. + 31 only
+      const int row = m0 + h * 128 + quad * 32 + lane;
 #pragma unroll 1
       for (int c = 0; c < kQmmBN / 32; ++c) {
         uint32_t v[32];
-        tmem_ld32(tmem + (uint32_t)(h * 128 + c * 32) + ((uint32_t)(warp * 32) << 16), v);
+        tmem_ld32(tmem + (uint32_t)(h * kQmmBN + c * 32) + ((uint32_t)(quad * 32) << 16), v);
         const int col = n0 + c * 32;
         if (row < a.M) {
           uint16_t* dst = a.y + (size_t)row * a.N + col;
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ 
           const uint64_t da0 = umma_desc_sw128(smA + s * kQmmAStage + h * 128 * 128);
 #pragma unroll
           for (int k4 = 0; k4 < kQmmBK / 16; ++k4)  // 16 bf16 = 32 bytes along K inside the swizzle atom: +2 units
-            umma_bf16(tmem + h * 128, da0 + 2 * k4, db0 + 2 * k4, kQmmIdesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+            umma_bf16(tmem + h * kQmmBN, da0 + 2 * k4, db0 + 2 * k4, kQmmIdesc, (kb > 0 || k4 > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);  // arrives when the MMAs above have read the stage
         if (kb == nk - 1) umma_commit(&accum_bar);
@@ -232,7 +238,7 @@ __global__ void __launch_bounds__(160, 1) qmm_tc_kernel(const __grid_constant__ 
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == 4)
+  if (warp == kQmmProducers / 32)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kQmmTmemCols) : "memory");
 }
 
@@ -240,8 +246,7 @@ cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, co
                           int M, int N, int K, int bits, cudaStream_t st) {
   QmmArgs a;
   a.y = y; a.x = x; a.wq = wq; a.scales = s; a.biases = b; a.M = M; a.N = N; a.K = K;
-  const int raw = 128 * 3 * ((kQmmBK * bits / 32) * 4 + 16);
-  const size_t smem = (size_t)kQmmSmem + raw;
+  const size_t smem = (size_t)kQmmSmem;
   static bool configured[2] = {false, false};
   const int idx = bits == 4 ? 0 : 1;
   if (!configured[idx]) {
@@ -252,8 +257,8 @@ cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, co
   }
   const dim3 grid((N + kQmmBN - 1) / kQmmBN, (M + kQmmBM - 1) / kQmmBM);
   count_launch();
-  if (bits == 4) qmm_tc_kernel<4><<<grid, 160, smem, st>>>(a);
-  else qmm_tc_kernel<8><<<grid, 160, smem, st>>>(a);
+  if (bits == 4) qmm_tc_kernel<4><<<grid, kQmmThreads, smem, st>>>(a);
+  else qmm_tc_kernel<8><<<grid, kQmmThreads, smem, st>>>(a);
   return cudaGetLastError();
 }
 
