@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--paged", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true", help="skip the prefill GEMM figure (BASELINE config 4 shapes)")
     return ap.parse_args()
 
 
@@ -295,10 +296,55 @@ def run_b200(a):
                             "launches_per_step": nlaunch, "avg_launch_us": round(qsec / nlaunch * 1e6, 2),
                             "algorithmic_bytes_per_launch": int(qbytes / nlaunch),
                             "how": "CUDA-event pair around each launch in an eager pass (no graph / PDL)"}
+    if not a.no_prefill and world == 1:
+        line["prefill_qmm"] = prefill_figure(margs, a.bits)
     if not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(margs, a.bits)
     print(json.dumps(line), flush=True)
     _finish(world)
+
+
+def prefill_figure(margs, bits, M=8192):
+    """Tensor-pipe figure of the prefill contraction (BASELINE config 4: 8k-token prompt): one layer's seven quantized
+    matmuls at M = 8192 through pie_qmm (tcgen05), useful flops 2*M*N*K, against the measured bf16 sustained peak."""
+    import torch
+    from proxy_inference_engine_b200 import ops
+    h, f = margs.hidden_size, margs.intermediate_size
+    nh, nkv, d = margs.num_attention_heads, margs.num_key_value_heads, margs.head_dim
+    shapes = [(nh * d, h), (nkv * d, h), (nkv * d, h), (h, nh * d), (f, h), (f, h), (h, f)]
+    mats, xs = [], {}
+    for n, k in shapes:
+        wq = torch.randint(-2**31, 2**31 - 1, (n, k * bits // 32), dtype=torch.int32, device="cuda")
+        s = (torch.rand((n, k // 64), device="cuda") * 0.01).to(torch.bfloat16)
+        b = (torch.rand((n, k // 64), device="cuda") * -0.05).to(torch.bfloat16)
+        xs.setdefault(k, torch.randn((M, k), device="cuda").to(torch.bfloat16))
+        mats.append((wq, s, b, k))
+
+    def layer():
+        for wq, s, b, k in mats:
+            ops.quantized_matmul(xs[k], wq, s, b, True, 64, bits)
+
+    for _ in range(3):
+        layer()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        layer()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    flops = 2 * M * sum(n * k for n, k in shapes)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            peak = float(json.load(fh)["bf16_tflops_sustained"])
+        src = "measured sustained (MEASURED_PEAKS.json)"
+    except Exception:
+        peak, src = 1400.0, "fallback (B200_PROFILING.md)"
+    tf = flops / ms / 1e9
+    return {"workload": f"one transformer layer's 7 quantized matmuls, M = {M} (8k-token prefill), q{bits}",
+            "kernel": f"qmm_tc_kernel<{bits}> (tcgen05.mma kind::f16, TMEM accumulators)", "ms_per_layer": round(ms, 3),
+            "achieved": round(tf, 1), "unit": "TFLOP/s", "peak": peak, "peak_source": src, "frac": round(tf / peak, 4),
+            "bound": "tensor"}
 
 
 def _finish(world):

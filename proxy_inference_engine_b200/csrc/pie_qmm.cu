@@ -78,6 +78,19 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// The BITS-wide field of `w` at bit `pos` lifted into an fp32 mantissa: 128 + q (4-bit) or 256 + q (8-bit), exactly,
+// with one shift and one LOP3 -- no integer-to-float conversion (those run on the 16-lane XU pipe).  The offset is
+// folded into the bias: w_hat = (off + q) * s + (b - off * s); the fold costs |off * s| * 2^-24, far below the
+// bf16 rounding of w_hat.
+template <int BITS>
+__device__ __forceinline__ float lift_f32(uint32_t w, int pos) {
+  constexpr int LSB = BITS == 4 ? 16 : 15;             // mantissa bit that weighs 1 at exponent 2^7 / 2^8
+  constexpr uint32_t MASK = ((1u << BITS) - 1u) << LSB;
+  constexpr uint32_t MAGIC = BITS == 4 ? 0x43000000u : 0x43800000u;
+  const uint32_t v = pos <= LSB ? (w << (LSB - pos)) : (w >> (pos - LSB));
+  return __uint_as_float((v & MASK) | MAGIC);
+}
+
 template <int BITS>
 __global__ void __launch_bounds__(kQmmThreads, 1) qmm_tc_kernel(const __grid_constant__ QmmArgs a) {
   constexpr int S = kQmmStages, LAG = 1;
@@ -134,7 +147,7 @@ __global__ void __launch_bounds__(kQmmThreads, 1) qmm_tc_kernel(const __grid_con
         uint4 wc[WPR / 4];
 #pragma unroll
         for (int c = 0; c < WPR / 4; ++c) wc[c] = wn[c];
-        const float sc = bf16lo(sn), bi = bf16lo(bn);
+        const float sc = bf16lo(sn), bb = fmaf(-(BITS == 4 ? 128.f : 256.f), sc, bf16lo(bn));
         if (kb + 1 < nk) {
 #pragma unroll
           for (int c = 0; c < WPR / 4; ++c) wn[c] = __ldg(wsrc + (size_t)(kb + 1) * (WPR / 4) + c);
@@ -150,8 +163,8 @@ __global__ void __launch_bounds__(kQmmThreads, 1) qmm_tc_kernel(const __grid_con
               uint32_t o[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                const float lo = fmaf((float)((w[i] >> (8 * e)) & 15u), sc, bi);
-                const float hi = fmaf((float)((w[i] >> (8 * e + 4)) & 15u), sc, bi);
+                const float lo = fmaf(lift_f32<4>(w[i], 8 * e), sc, bb);
+                const float hi = fmaf(lift_f32<4>(w[i], 8 * e + 4), sc, bb);
                 o[e] = pack_bf16(lo, hi);
               }
               const uint32_t c = (uint32_t)(c4 * 4 + i);
@@ -165,8 +178,8 @@ __global__ void __launch_bounds__(kQmmThreads, 1) qmm_tc_kernel(const __grid_con
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const uint32_t ww = w[2 * i + (e >> 1)];
-                const float lo = fmaf((float)((ww >> (16 * (e & 1))) & 255u), sc, bi);
-                const float hi = fmaf((float)((ww >> (16 * (e & 1) + 8)) & 255u), sc, bi);
+                const float lo = fmaf(lift_f32<8>(ww, 16 * (e & 1)), sc, bb);
+                const float hi = fmaf(lift_f32<8>(ww, 16 * (e & 1) + 8), sc, bb);
                 o[e] = pack_bf16(lo, hi);
               }
               const uint32_t c = (uint32_t)(c4 * 2 + i);

@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, the bench line, the ncu launch list and one full capture of the dominant kernel.
+# One GPU-box visit: parity tests, the bench lines, the ncu launch list and full captures of the dominant kernels.
 # Usage (from the repo root, under gpurun):  bash tools/gpu_round.sh [tag]
 TAG=${1:-r01}
 OUT=gpurun_out/$TAG
@@ -10,12 +10,19 @@ echo "pytest exit $?" >> $OUT/pytest_gpu.log
 ( time timeout 900 python bench.py ) > $OUT/bench.log 2> $OUT/bench.err
 echo "bench exit $?" >> $OUT/bench.err
 ( time timeout 600 python bench.py --impl reference --steps 2 --warmup 1 ) > $OUT/bench_ref.log 2> $OUT/bench_ref.err
-CMD="python bench.py --steps 2 --warmup 3 --prompt 8 --no-cpu-baseline --no-kernel-timing"
+timeout 300 python tools/bench_qmm.py > $OUT/qmm_q4.json 2>&1
+timeout 300 python tools/bench_qmm.py --bits 8 > $OUT/qmm_q8.json 2>&1
+timeout 300 python tools/bench_qmv.py --M 1 --graph 40 --pdl 1 > $OUT/qmv_m1.json 2>&1
+timeout 300 python tools/bench_step_parts.py > $OUT/step_parts.json 2>&1
+CMD="python bench.py --steps 2 --warmup 3 --prompt 8 --no-cpu-baseline --no-kernel-timing --no-prefill"
 timeout 600 $CMD > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:pie:: -c 1500 \
     --csv --log-file $OUT/launches.csv $CMD > $OUT/ncu_list.log 2>&1
 timeout 600 $CMD > $OUT/plain2.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:qmv_kernel -s 400 -c 6 \
     -o $OUT/prof_qmv $CMD > $OUT/ncu_full.log 2>&1
+timeout 300 python tools/bench_qmm.py --iters 1 > /dev/null 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:qmm_tc_kernel -s 8 -c 2 \
+    -o $OUT/prof_qmm python tools/bench_qmm.py --iters 1 > $OUT/ncu_qmm.log 2>&1
 ls -la $OUT
-tail -3 $OUT/pytest_gpu.log; cat $OUT/bench.log; tail -3 $OUT/bench.err; cat $OUT/bench_ref.log
+tail -3 $OUT/pytest_gpu.log; cat $OUT/bench.log; tail -3 $OUT/bench.err; cat $OUT/bench_ref.log; cat $OUT/qmm_q4.json
