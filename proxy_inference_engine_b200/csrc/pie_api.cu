@@ -49,7 +49,7 @@ QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksp
   }
   if (p.ksplit == 0) p.ksplit = chunks;  // cannot happen for M <= 32 (one chunk of x is <= 16 KB)
   p.kslice = K / p.ksplit;
-  int ncta = sms / p.ksplit;
+  int ncta = sms * env_int("PIE_QMV_CTAS_PER_SM", 1) / p.ksplit;  // > 1 only with PIE_QMV_WARPS=8 (experiment)
   if (ncta > p.ntiles) ncta = p.ntiles;
   if (ncta < 1) ncta = 1;
   p.grid = ncta * p.ksplit;

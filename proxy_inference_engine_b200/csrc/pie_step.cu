@@ -88,6 +88,17 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// fp32 at shared-memory address `local_addr` of CTA `rank` of this cluster (distributed shared memory)
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, int rank) {
+  uint32_t remote;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+  return v;
+}
 __device__ __forceinline__ size_t step_kv_addr(const KvLayout& kv, int b, int h, int t) {
   if (kv.page_table) {
     const int page = __ldg(kv.page_table + (size_t)b * kv.pt_stride + t / kv.page_size);
@@ -131,7 +142,10 @@ __device__ __forceinline__ void rope_row(float* v, const float* sn, const float*
 // round.  The token being appended is taken from the q/k/v projection output (rotated in registers and written to
 // the cache by the rgi == 0 unit); older tokens come from the cache.  Split partials are merged in split order by
 // the last unit to arrive, as in decode_attn_kernel (pie_attn.cu).
-template <int D, int R>
+// CLUSTER: the splits of one (row, kv head, head group) are the CTAs of one thread-block cluster (stand-alone launch,
+// nsplit <= 8): their partials meet through distributed shared memory behind a cluster barrier instead of a global
+// workspace + fence + atomic + re-read, and every CTA of the cluster finishes a slice of the output.
+template <int D, int R, bool CLUSTER>
 __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag) {
   constexpr int C = D / 64, E = 8 * C, PW = D + 2, NW = kStepWarps;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, tg = lane >> 3;
@@ -144,6 +158,17 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
     const int kvh = rest % s.Hkv;
     const int b = rest / s.Hkv;
     const int qh0 = kvh * (s.rg * R) + rgi * R;
+    // everything that does not depend on the position is requested first: one round trip for pos, freqs and q
+    const uint16_t* row = P.qkv + (size_t)b * qkv_ld;
+    uint4 qraw[R][C];
+    float fr[8];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int c = 0; c < C; ++c)
+        qraw[r][c] = ldcg128(reinterpret_cast<const uint4*>(row + (size_t)(qh0 + r) * D) + sub + 8 * c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) fr[j] = __ldg(s.freqs + (C == 2 ? 8 * sub : 8 * (sub & 3)) + j);
     const int p = s.pos[b], ctx = p + 1;
     const int per = (ctx + s.nsplit - 1) / s.nsplit;
     const int t0 = split * per, t1 = min(ctx, t0 + per);
@@ -151,17 +176,12 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
     if (t0 < t1) {
       float sn[8], cs[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int i = (C == 2 ? 8 * sub : 8 * (sub & 3)) + j;
-        sincosf((float)p * (1.0f / __ldg(s.freqs + i)), &sn[j], &cs[j]);
-      }
-      const uint16_t* row = P.qkv + (size_t)b * qkv_ld;
+      for (int j = 0; j < 8; ++j) sincosf((float)p * (1.0f / fr[j]), &sn[j], &cs[j]);
       float q[R][E];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const uint4* qp = reinterpret_cast<const uint4*>(row + (size_t)(qh0 + r) * D);
 #pragma unroll
-        for (int c = 0; c < C; ++c) unpack8(ldcg128(qp + sub + 8 * c), &q[r][8 * c]);
+        for (int c = 0; c < C; ++c) unpack8(qraw[r][c], &q[r][8 * c]);
         rope_row<C>(q[r], sn, cs, sub);
 #pragma unroll
         for (int e = 0; e < E; ++e) q[r][e] *= s.scale_log2e;
@@ -270,13 +290,35 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
       }
       if (s.nsplit == 1) {
         P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+      } else if (CLUSTER) {
+        float* rec = scratch + (size_t)NW * R * PW + (size_t)r * PW;  // this CTA's partial, read by its cluster peers
+        rec[d] = at;
+        if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
       } else {
         float* rec = s.attn_part + (rec0 + (size_t)r * s.nsplit + split) * PW;
         rec[d] = at;
         if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
       }
     }
-    if (s.nsplit > 1) {
+    if (CLUSTER && s.nsplit > 1) {
+      cluster_sync();  // release / acquire: every split's partial is in its CTA's shared memory
+      const uint32_t mine = smem_u32(scratch + (size_t)NW * R * PW);
+      for (int i = threadIdx.x * s.nsplit + split; i < R * D; i += blockDim.x * s.nsplit) {  // this CTA's slice
+        const int r = i / D, d = i % D;
+        float mn = -INFINITY;
+        for (int sp = 0; sp < s.nsplit; ++sp) mn = fmaxf(mn, ld_dsmem_f32(mine + (r * PW + D) * 4, sp));
+        float lt = 0.f, at = 0.f;
+        for (int sp = 0; sp < s.nsplit; ++sp) {  // split order: deterministic
+          const float ms = ld_dsmem_f32(mine + (r * PW + D) * 4, sp);
+          const float cw = ms == -INFINITY ? 0.f : exp2f(ms - mn);
+          lt += ld_dsmem_f32(mine + (r * PW + D + 1) * 4, sp) * cw;
+          at += ld_dsmem_f32(mine + (r * PW + d) * 4, sp) * cw;
+        }
+        P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+      }
+      cluster_sync();  // no CTA leaves (or reuses its partial) while a peer may still read it
+    }
+    if (!CLUSTER && s.nsplit > 1) {
       __threadfence();
       __syncthreads();
       const int cidx = (b * s.Hkv + kvh) * s.rg + rgi;
@@ -365,14 +407,14 @@ __device__ __noinline__ void argmax_phase(const StepArgs& s, float* sv, int* si)
 }
 
 // Stand-alone form of the attention phase: one CTA per unit (pie_decode_attn_fused).
-template <int D, int R>
+template <int D, int R, bool CLUSTER>
 __global__ void __launch_bounds__(kStepWarps * 32, 1) attn_fused_kernel(const __grid_constant__ StepArgs s,
                                                                        const __grid_constant__ StepPhase P) {
-  __shared__ float scratch[kStepWarps * R * (D + 2)];
+  __shared__ float scratch[(kStepWarps + 1) * R * (D + 2)];
   __shared__ int s_flag;
   pdl_launch_dependents();
   pdl_wait();
-  attn_phase<D, R>(s, P, scratch, &s_flag);
+  attn_phase<D, R, CLUSTER>(s, P, scratch, &s_flag);
 }
 
 // The main loop of one matrix of the step.  Not inlined and free of calls: it needs the whole register file.
@@ -405,11 +447,11 @@ __global__ void __launch_bounds__(kStepWarps * 32, 1) decode_step_kernel(const _
     } else if (P.pre == PRE_ATTN) {
       grid_barrier(s.bar);
       if (s.D == 128) {
-        if (s.R == 2) attn_phase<128, 2>(s, P, scratch, &s_flag);
-        else attn_phase<128, 1>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<128, 2, false>(s, P, scratch, &s_flag);
+        else attn_phase<128, 1, false>(s, P, scratch, &s_flag);
       } else {
-        if (s.R == 2) attn_phase<64, 2>(s, P, scratch, &s_flag);
-        else attn_phase<64, 1>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<64, 2, false>(s, P, scratch, &s_flag);
+        else attn_phase<64, 1, false>(s, P, scratch, &s_flag);
       }
     }
     grid_barrier(s.bar);
@@ -592,15 +634,32 @@ int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache
   cfg.gridDim = dim3((unsigned)(B * Hkv * s.rg * nsplit), 1, 1);
   cfg.blockDim = dim3(kStepWarps * 32, 1, 1);
   cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  // 2..8 splits: the splits of a unit form one thread-block cluster and merge through distributed shared memory
+  const bool cluster = nsplit > 1 && nsplit <= 8;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cluster) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)nsplit;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl ? 1 : 0;
+  cfg.numAttrs = na;
   count_launch();
   cudaError_t e;
-  if (D == 128) e = R == 2 ? cudaLaunchKernelEx(&cfg, attn_fused_kernel<128, 2>, s, P) : cudaLaunchKernelEx(&cfg, attn_fused_kernel<128, 1>, s, P);
-  else e = R == 2 ? cudaLaunchKernelEx(&cfg, attn_fused_kernel<64, 2>, s, P) : cudaLaunchKernelEx(&cfg, attn_fused_kernel<64, 1>, s, P);
+#define PIE_ATTN_LAUNCH(DD, RR)                                                                  \
+  (cluster ? cudaLaunchKernelEx(&cfg, attn_fused_kernel<DD, RR, true>, s, P)                     \
+           : cudaLaunchKernelEx(&cfg, attn_fused_kernel<DD, RR, false>, s, P))
+  if (D == 128) e = R == 2 ? PIE_ATTN_LAUNCH(128, 2) : PIE_ATTN_LAUNCH(128, 1);
+  else e = R == 2 ? PIE_ATTN_LAUNCH(64, 2) : PIE_ATTN_LAUNCH(64, 1);
+#undef PIE_ATTN_LAUNCH
   return status_of(e);
 }
 

@@ -17,6 +17,7 @@ Token ids and positions stay on the device; the host reads the token list back w
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -93,7 +94,11 @@ class DecodeEngine:
         self.nsplit = L.pie_decode_attn_pick_splits(B, self.Hq, self.Hkv, max_context)
         # rope + KV append + flash-decode in one launch (pie_decode_attn_fused) unless asked for the three-operator form
         self.attn_fused = attn_fused
-        self.nsplit_fused = L.pie_decode_step_pick_splits(B, self.Hq, self.Hkv, max_context)
+        # the splits of a unit form one thread-block cluster and merge through distributed shared memory; measured on
+        # B200 (8B, bs1): 3..6 splits cost the same, clusters of 8 are markedly slower to schedule -> cap at 6
+        self.nsplit_fused = min(6, L.pie_decode_step_pick_splits(B, self.Hq, self.Hkv, max_context))
+        if os.environ.get("PIE_ATTN_SPLITS"):  # tuning knob (tools/bench_step_parts.py)
+            self.nsplit_fused = int(os.environ["PIE_ATTN_SPLITS"])
         nb = L.pie_decode_attn_workspace_bytes(B, self.Hq, self.D, max(self.nsplit, self.nsplit_fused))
         self.attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
         # per-layer segment tables (host structs must outlive the captured graph: keep references)

@@ -15,7 +15,8 @@ over = {"num_hidden_layers": a.layers} if a.layers else {}
 margs = preset_args(a.model, bits=a.bits, **over)
 model = build_model(margs, random_weights(margs, seed=0, device="cuda"))
 res = {}
-for skip in ("", "rope", "attn", "rope,attn", "rope,attn,o,qkv", "rope,attn,o,qkv,gu", "rope,attn,o,qkv,gu,down"):
+ap2 = os.environ.get("PIE_PARTS", "")
+for skip in (tuple(ap2.split(";")) if ap2 else ("", "rope", "attn", "rope,attn", "rope,attn,o,qkv", "rope,attn,o,qkv,gu", "rope,attn,o,qkv,gu,down")):
     os.environ["PIE_DEBUG_SKIP"] = skip
     eng = dec.DecodeEngine(model, batch=a.batch, max_context=a.ctx + 200)
     eng.positions.fill_(a.ctx); eng.tokens.fill_(5)
