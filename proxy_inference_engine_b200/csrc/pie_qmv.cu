@@ -40,5 +40,17 @@ __global__ void __launch_bounds__(MT == 4 ? 256 : 512, 1) qmv_kernel(const __gri
   qmv_body<BITS, MT, ONECOL, false, QMV_FULL>(a, smem, false, [] { pdl_launch_dependents(); pdl_wait(); });
 }
 
+// Experiment (PIE_QMV_SMEMARGS=1, tools/bench_qmv.py): the same matrix with the descriptor read from shared memory
+// and the producer words parked in shared memory, i.e. the GEMV exactly as the one-launch decode step runs it.
+template <int BITS>
+__global__ void __launch_bounds__(512, 1) qmv_kernel_smemargs(const __grid_constant__ QmvArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ QmvArgs sa;
+  for (int i = threadIdx.x; i < (int)(sizeof(QmvArgs) / 4); i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&sa)[i] = reinterpret_cast<const uint32_t*>(&a)[i];
+  __syncthreads();
+  qmv_body<BITS, 1, true, true, QMV_FULL>(sa, smem, false, [] { pdl_launch_dependents(); pdl_wait(); });
+}
+
 }  // namespace pie
 #include "pie_qmv_launch.inl"

@@ -1,4 +1,5 @@
 // Launcher of the decode GEMV and the slow generic kernel for shapes off the fast path.
+#include <cstdlib>
 namespace pie {
 
 int qmv_mt(int M) { return M <= 8 ? 1 : (M <= 16 ? 2 : 4); }
@@ -40,8 +41,33 @@ static cudaError_t launch_qmv_t(const QmvArgs& a, int warps, int grid, bool pdl,
   return cudaLaunchKernelEx(&cfg, qmv_kernel<BITS, MT, ONECOL>, a);
 }
 
+static cudaError_t launch_qmv_smemargs(const QmvArgs& a, int warps, int grid, bool pdl, cudaStream_t st) {
+  const size_t smem = qmv_smem_bytes(a.M, a.kslice, 4, warps, 1) + (size_t)warps * 32 * kQmvProdWords * 4;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(qmv_kernel_smemargs<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kQmvMaxSmem - 1024);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3((unsigned)warps * 32, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, qmv_kernel_smemargs<4>, a);
+}
+
 cudaError_t launch_qmv(const QmvArgs& a, int bits, int warps, int grid, bool pdl, cudaStream_t st) {
   const int mt = qmv_mt(a.M);
+  static const bool smemargs = getenv("PIE_QMV_SMEMARGS") && atoi(getenv("PIE_QMV_SMEMARGS")) != 0;
+  if (smemargs && bits == 4 && a.M == 1 && warps == 16) return launch_qmv_smemargs(a, warps, grid, pdl, st);
   if (bits == 4) {
     if (a.M == 1) return launch_qmv_t<4, 1, true>(a, warps, grid, pdl, st);
     if (mt == 1) return launch_qmv_t<4, 1, false>(a, warps, grid, pdl, st);
