@@ -145,9 +145,9 @@ __device__ __forceinline__ void rope_row(float* v, const float* sn, const float*
 // CLUSTER: the splits of one (row, kv head, head group) are the CTAs of one thread-block cluster (stand-alone launch,
 // nsplit <= 8): their partials meet through distributed shared memory behind a cluster barrier instead of a global
 // workspace + fence + atomic + re-read, and every CTA of the cluster finishes a slice of the output.
-template <int D, int R, bool CLUSTER>
+template <int D, int R, bool CLUSTER, int NW>
 __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag) {
-  constexpr int C = D / 64, E = 8 * C, PW = D + 2, NW = kStepWarps;
+  constexpr int C = D / 64, E = 8 * C, PW = D + 2;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, tg = lane >> 3;
   const int units = s.B * s.Hkv * s.rg * s.nsplit;
   const int qkv_ld = (s.Hq + 2 * s.Hkv) * D;
@@ -193,6 +193,22 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[r][e] = 0.f;
       }
+      // K/V rows of the NEXT round are requested before the current round is used: one round trip hidden per round
+      uint4 kn[C], vn[C];
+      auto request = [&](int tb_) {
+        const int t_ = tb_ + tg;
+        if (t_ < t1) {
+          const bool fresh_ = t_ == p;
+          const size_t off = step_kv_addr(P.kv, b, kvh, t_);
+          const uint4* kp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + kvh) * D)
+                                   : reinterpret_cast<const uint4*>(P.kc + off);
+          const uint4* vp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + s.Hkv + kvh) * D)
+                                   : reinterpret_cast<const uint4*>(P.vc + off);
+#pragma unroll
+          for (int c = 0; c < C; ++c) { kn[c] = ldcg128(kp + sub + 8 * c); vn[c] = ldcg128(vp + sub + 8 * c); }
+        }
+      };
+      if (t0 + warp * 4 < t1) request(t0 + warp * 4);
       for (int tb = t0 + warp * 4; tb < t1; tb += NW * 4) {  // warp-uniform trip count; tail lanes idle
         const int t = tb + tg;
         const bool ok = t < t1;
@@ -201,14 +217,10 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
         for (int e = 0; e < E; ++e) { kf[e] = 0.f; vf[e] = 0.f; }
         const bool fresh = ok && t == p;  // the token of this step: not in the cache yet
         uint4 kr[C], vr[C];
-        if (ok) {
-          const size_t off = step_kv_addr(P.kv, b, kvh, t);
-          const uint4* kp = fresh ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + kvh) * D)
-                                  : reinterpret_cast<const uint4*>(P.kc + off);
-          const uint4* vp = fresh ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + s.Hkv + kvh) * D)
-                                  : reinterpret_cast<const uint4*>(P.vc + off);
 #pragma unroll
-          for (int c = 0; c < C; ++c) { kr[c] = ldcg128(kp + sub + 8 * c); vr[c] = ldcg128(vp + sub + 8 * c); }
+        for (int c = 0; c < C; ++c) { kr[c] = kn[c]; vr[c] = vn[c]; }
+        if (tb + NW * 4 < t1) request(tb + NW * 4);
+        if (ok) {
 #pragma unroll
           for (int c = 0; c < C; ++c) { unpack8(kr[c], &kf[8 * c]); unpack8(vr[c], &vf[8 * c]); }
         }
@@ -407,14 +419,15 @@ __device__ __noinline__ void argmax_phase(const StepArgs& s, float* sv, int* si)
 }
 
 // Stand-alone form of the attention phase: one CTA per unit (pie_decode_attn_fused).
+constexpr int kAttnWarps = 8;  // stand-alone launch: 8 warps and up to 255 registers (no spills, K/V double-buffered)
 template <int D, int R, bool CLUSTER>
-__global__ void __launch_bounds__(kStepWarps * 32, 1) attn_fused_kernel(const __grid_constant__ StepArgs s,
+__global__ void __launch_bounds__(kAttnWarps * 32, 1) attn_fused_kernel(const __grid_constant__ StepArgs s,
                                                                        const __grid_constant__ StepPhase P) {
-  __shared__ float scratch[(kStepWarps + 1) * R * (D + 2)];
+  __shared__ float scratch[(kAttnWarps + 1) * R * (D + 2)];
   __shared__ int s_flag;
   pdl_launch_dependents();
   pdl_wait();
-  attn_phase<D, R, CLUSTER>(s, P, scratch, &s_flag);
+  attn_phase<D, R, CLUSTER, kAttnWarps>(s, P, scratch, &s_flag);
 }
 
 // The main loop of one matrix of the step.  Not inlined and free of calls: it needs the whole register file.
@@ -447,11 +460,11 @@ __global__ void __launch_bounds__(kStepWarps * 32, 1) decode_step_kernel(const _
     } else if (P.pre == PRE_ATTN) {
       grid_barrier(s.bar);
       if (s.D == 128) {
-        if (s.R == 2) attn_phase<128, 2, false>(s, P, scratch, &s_flag);
-        else attn_phase<128, 1, false>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<128, 2, false, kStepWarps>(s, P, scratch, &s_flag);
+        else attn_phase<128, 1, false, kStepWarps>(s, P, scratch, &s_flag);
       } else {
-        if (s.R == 2) attn_phase<64, 2, false>(s, P, scratch, &s_flag);
-        else attn_phase<64, 1, false>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<64, 2, false, kStepWarps>(s, P, scratch, &s_flag);
+        else attn_phase<64, 1, false, kStepWarps>(s, P, scratch, &s_flag);
       }
     }
     grid_barrier(s.bar);
@@ -632,7 +645,7 @@ int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache
   P.kv.page_table = kv->page_table; P.kv.pt_stride = kv->pt_stride; P.kv.page_size = kv->page_size;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(B * Hkv * s.rg * nsplit), 1, 1);
-  cfg.blockDim = dim3(kStepWarps * 32, 1, 1);
+  cfg.blockDim = dim3(kAttnWarps * 32, 1, 1);
   cfg.stream = (cudaStream_t)stream;
   // 2..8 splits: the splits of a unit form one thread-block cluster and merge through distributed shared memory
   const bool cluster = nsplit > 1 && nsplit <= 8;
