@@ -83,6 +83,8 @@ cudaError_t launch_prefill_attn(uint16_t* out, const uint16_t* q, const uint16_t
                                 const KvLayout& kv, int B, int Hq, int Hkv, int L, int D, int offset,
                                 float scale, cudaStream_t st) {
   if (B == 0 || L == 0) return cudaSuccess;
+  static const bool naive = [] { const char* e = getenv("PIE_PREFILL_ATTN_NAIVE"); return e && e[0] == '1'; }();
+  if (!naive) return launch_prefill_attn_tc(out, q, kc, vc, kv, B, Hq, Hkv, L, D, offset, scale, st);
   const float sl = scale * 1.4426950408889634f;
   const dim3 grid(L, Hq, B);
   count_launch();

@@ -1,0 +1,208 @@
+// Prefill attention (L > 1, causal) on tensor cores, sm_100a.
+//
+// Replaces mx.fast.scaled_dot_product_attention with the additive causal mask of create_attention_mask
+// (PIE/models/base.py:18-53, 92-113; Metal steel_attention, MLX/mlx/backend/metal/scaled_dot_product_attention.cpp:
+// 16-131): out[b, l, h] = softmax(scale * q[b,h,l] . K[b, h / n_rep, :offset+l+1]) . V.  The mask value -1e9 makes
+// masked probabilities exactly 0 in fp32, so masked keys are skipped (tiles beyond the diagonal are never loaded).
+//
+// Flash-attention forward: a CTA of 4 warps owns 64 query rows of one head (16 per warp, Q fragments in registers);
+// K / V tiles of 64 keys stream through a double-buffered, XOR-swizzled shared-memory stage (cp.async, straight from
+// the contiguous or paged cache); S = Q K^T and O += P V run on mma.sync.m16n8k16 (bf16 in, fp32 accumulate) with
+// ldmatrix / ldmatrix.trans operand loads; the softmax is online in fp32 (exp2 on log2e-prescaled scores); P is
+// rounded to bf16 for the second product.  GQA: the n_rep query heads of a kv head are separate CTAs; their K/V tiles
+// come from L2.
+#include "pie_internal.h"
+#include "pie_ptx.cuh"
+
+namespace pie {
+
+constexpr int kFaBQ = 64, kFaBKV = 64, kFaThreads = 128;
+
+__device__ __forceinline__ size_t fa_kv_addr(const KvLayout& kv, int b, int h, int t) {
+  if (kv.page_table) {
+    const int page = __ldg(kv.page_table + (size_t)b * kv.pt_stride + t / kv.page_size);
+    return ((size_t)page * kv.page_size + t % kv.page_size) * kv.tok_stride + (size_t)h * kv.head_stride;
+  }
+  return (size_t)b * kv.batch_stride + (size_t)h * kv.head_stride + (size_t)t * kv.tok_stride;
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr) : "memory");
+}
+
+struct FaArgs {
+  uint16_t* out;
+  const uint16_t* q;
+  const uint16_t* kc;
+  const uint16_t* vc;
+  KvLayout kv;
+  int Hq, Hkv, L, offset;
+  float scale_log2e;
+};
+
+// shared-memory tile [64 keys][D] bf16; the 16-byte chunk c of row r sits at chunk (c ^ (r & 7)): ldmatrix reads of
+// 8 consecutive rows at one logical chunk hit 8 different bank groups
+template <int D>
+__device__ __forceinline__ uint32_t fa_tile_off(int r, int c) {
+  return (uint32_t)(r * (D * 2) + ((c ^ (r & 7)) << 4));
+}
+
+template <int D>
+__global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_constant__ FaArgs a) {
+  constexpr int KC = D / 16;   // k chunks of the S product (over head features)
+  constexpr int NT = kFaBKV / 8;  // n tiles of S (keys)
+  constexpr int DT = D / 8;    // n tiles of O (head features)
+  constexpr int CPR = D / 8;   // 16-byte chunks per tile row
+  constexpr int TILE = kFaBKV * D * 2;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t4 = lane & 3;
+  const int q0 = blockIdx.x * kFaBQ, h = blockIdx.y, b = blockIdx.z;
+  const int kvh = h / (a.Hq / a.Hkv);
+  const int T = a.offset + a.L;
+  const uint32_t sK = smem_u32(smem), sV = sK + 2 * TILE;
+
+  // keys this CTA needs: 0 .. offset + min(q0 + 63, L - 1)
+  const int last_key = a.offset + min(q0 + kFaBQ, a.L) - 1;
+  const int ntiles = last_key / kFaBKV + 1;
+
+  auto issue = [&](int j) {
+    const uint32_t dk = sK + (j & 1) * TILE, dv = sV + (j & 1) * TILE;
+    for (int i = tid; i < kFaBKV * CPR; i += kFaThreads) {
+      const int r = i / CPR, c = i % CPR;
+      const int t = min(j * kFaBKV + r, T - 1);
+      const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
+      cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
+      cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+    }
+    cp_async_commit();
+  };
+  issue(0);
+
+  // Q fragments (A operand, 16 rows x D per warp): rows q0 + 16 warp + g and + 8, straight from global memory
+  const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+  const uint16_t* qb = a.q + ((size_t)b * a.Hq + h) * a.L * D;
+  const uint32_t* qr0 = reinterpret_cast<const uint32_t*>(qb + (size_t)min(r0, a.L - 1) * D);
+  const uint32_t* qr1 = reinterpret_cast<const uint32_t*>(qb + (size_t)min(r1, a.L - 1) * D);
+  uint32_t qf[KC][4];
+#pragma unroll
+  for (int kc = 0; kc < KC; ++kc) {
+    qf[kc][0] = __ldg(qr0 + kc * 8 + t4);
+    qf[kc][1] = __ldg(qr1 + kc * 8 + t4);
+    qf[kc][2] = __ldg(qr0 + kc * 8 + 4 + t4);
+    qf[kc][3] = __ldg(qr1 + kc * 8 + 4 + t4);
+  }
+  float o[DT][4];
+#pragma unroll
+  for (int i = 0; i < DT; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  const int lim0 = a.offset + r0, lim1 = a.offset + r1;  // last key each of this thread's two rows may see
+
+  for (int j = 0; j < ntiles; ++j) {
+    if (j + 1 < ntiles) { issue(j + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const uint32_t tk = sK + (j & 1) * TILE, tv = sV + (j & 1) * TILE;
+    // ---- S = Q K^T : 16 x 64 per warp ----------------------------------------------------------------------
+    float s[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) { s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f; }
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+#pragma unroll
+      for (int kc = 0; kc < KC; kc += 2) {
+        // 4 matrices: (keys 8n.., features 16kc..+8), (.. +8..+16), (16(kc+1)..+8), (.. +8..+16)
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(tk + fa_tile_off<D>(n * 8 + (lane & 7), kc * 2 + (lane >> 3)), b0, b1, b2, b3);
+        mma_bf16_16816(s[n], qf[kc][0], qf[kc][1], qf[kc][2], qf[kc][3], b0, b1);
+        mma_bf16_16816(s[n], qf[kc + 1][0], qf[kc + 1][1], qf[kc + 1][2], qf[kc + 1][3], b2, b3);
+      }
+    }
+    // ---- scale, causal mask, online softmax ------------------------------------------------------------------
+    const int key0 = j * kFaBKV + 2 * t4;
+    const bool diag = j * kFaBKV + kFaBKV - 1 > a.offset + q0 + warp * 16;  // some key of the tile may be masked
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s[n][e] *= a.scale_log2e;
+      if (diag) {
+        const int k = key0 + n * 8;
+        if (k > lim0) s[n][0] = -INFINITY;
+        if (k + 1 > lim0) s[n][1] = -INFINITY;
+        if (k > lim1) s[n][2] = -INFINITY;
+        if (k + 1 > lim1) s[n][3] = -INFINITY;
+      }
+      mx0 = fmaxf(mx0, fmaxf(s[n][0], s[n][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[n][2], s[n][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float c0 = mn0 == -INFINITY ? 1.f : exp2f(m0 - mn0), c1 = mn1 == -INFINITY ? 1.f : exp2f(m1 - mn1);
+    const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
+    float ps0 = 0.f, ps1 = 0.f;
+    uint32_t pf[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      const float p0 = exp2f(s[n][0] - ms0), p1 = exp2f(s[n][1] - ms0);
+      const float p2 = exp2f(s[n][2] - ms1), p3 = exp2f(s[n][3] - ms1);
+      ps0 += p0 + p1; ps1 += p2 + p3;
+      pf[n][0] = pack_bf16(p0, p1);
+      pf[n][1] = pack_bf16(p2, p3);
+    }
+    l0 = l0 * c0 + ps0; l1 = l1 * c1 + ps1;
+    m0 = mn0; m1 = mn1;
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+    // ---- O += P V : contraction over the tile's 64 keys ------------------------------------------------------
+#pragma unroll
+    for (int kk = 0; kk < kFaBKV / 16; ++kk) {
+      const uint32_t a0 = pf[2 * kk][0], a1 = pf[2 * kk][1], a2 = pf[2 * kk + 1][0], a3 = pf[2 * kk + 1][1];
+#pragma unroll
+      for (int dj = 0; dj < DT; dj += 2) {
+        // transposed 8x8 blocks: (keys 16kk..+8, features 8dj..), (keys +8..+16, 8dj..), (keys lo, 8(dj+1)..), (keys hi, ..)
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_trans(tv + fa_tile_off<D>(kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, dj + (lane >> 4)), b0, b1, b2, b3);
+        mma_bf16_16816(o[dj], a0, a1, a2, a3, b0, b1);
+        mma_bf16_16816(o[dj + 1], a0, a1, a2, a3, b2, b3);
+      }
+    }
+    __syncthreads();  // the stage is refilled two iterations from now
+  }
+  // ---- finish: row sums over the 4 lanes of a row, normalise, bf16 store [B, L, Hq * D] --------------------------
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float i0 = 1.f / l0, i1 = 1.f / l1;
+  uint16_t* ob = a.out + ((size_t)b * a.L) * a.Hq * D + (size_t)h * D;
+#pragma unroll
+  for (int i = 0; i < DT; ++i) {
+    const int d = i * 8 + 2 * t4;
+    if (r0 < a.L) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * a.Hq * D + d) = pack_bf16(o[i][0] * i0, o[i][1] * i0);
+    if (r1 < a.L) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * a.Hq * D + d) = pack_bf16(o[i][2] * i1, o[i][3] * i1);
+  }
+}
+
+cudaError_t launch_prefill_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
+                                   const KvLayout& kv, int B, int Hq, int Hkv, int L, int D, int offset, float scale,
+                                   cudaStream_t st) {
+  FaArgs a;
+  a.out = out; a.q = q; a.kc = kc; a.vc = vc; a.kv = kv; a.Hq = Hq; a.Hkv = Hkv; a.L = L; a.offset = offset;
+  a.scale_log2e = scale * 1.4426950408889634f;
+  const size_t smem = (size_t)4 * kFaBKV * D * 2;  // K and V, double-buffered
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(fa_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kFaBKV * 128 * 2);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const dim3 grid((L + kFaBQ - 1) / kFaBQ, Hq, B);
+  count_launch();
+  if (D == 128) fa_prefill_kernel<128><<<grid, kFaThreads, smem, st>>>(a);
+  else fa_prefill_kernel<64><<<grid, kFaThreads, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace pie

@@ -80,7 +80,9 @@ def test_paged_attention_matches_contiguous(env):
     assert rel_l2(got.reshape(B, Hq, D), ref) < 3e-3
 
 
-@pytest.mark.parametrize("B,Hq,Hkv,D,L,off", [(1, 4, 2, 64, 16, 0), (2, 8, 2, 128, 33, 0), (1, 8, 8, 128, 5, 40)])
+@pytest.mark.parametrize("B,Hq,Hkv,D,L,off", [(1, 4, 2, 64, 16, 0), (2, 8, 2, 128, 33, 0), (1, 8, 8, 128, 5, 40),
+                                              (1, 4, 2, 128, 300, 0), (2, 4, 1, 128, 150, 77), (1, 2, 2, 64, 257, 63),
+                                              (1, 8, 2, 128, 64, 64)])
 def test_sdpa_prefill_causal(env, B, Hq, Hkv, D, L, off):
     orc, ops = env
     rng = np.random.default_rng(L + off)
