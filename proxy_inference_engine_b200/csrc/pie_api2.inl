@@ -78,12 +78,19 @@ size_t pie_decode_attn_workspace_bytes(int B, int Hq, int D, int nsplit) {
 int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context) {
   if (B <= 0 || Hq <= 0 || Hkv <= 0) return 1;
   const int n_rep = Hq / Hkv;
-  const int rg = n_rep % 4 == 0 ? n_rep / 4 : (n_rep % 2 == 0 ? n_rep / 2 : n_rep);
-  const int ctas = B * Hkv * rg;
-  int ns = (148 * 4 + ctas - 1) / ctas;
-  const int cap = (max_context + 63) / 64;  // >= 64 tokens per split
+  int ctas, want;
+  if (n_rep <= 16) {  // tensor-core kernel: one CTA per (sequence, kv head, split), 3 resident per SM
+    ctas = B * Hkv;
+    want = 148 * 3;
+  } else {
+    const int rg = n_rep % 4 == 0 ? n_rep / 4 : (n_rep % 2 == 0 ? n_rep / 2 : n_rep);
+    ctas = B * Hkv * rg;
+    want = 148 * 4;
+  }
+  int ns = (want + ctas - 1) / ctas;
+  const int cap = (max_context + 63) / 64;  // >= 64 tokens (one stage) per split
   if (ns > cap) ns = cap;
-  if (ns > 64) ns = 64;
+  if (ns > 32) ns = 32;  // kFaMaxSplits (pie_fa.cu)
   return ns < 1 ? 1 : ns;
 }
 

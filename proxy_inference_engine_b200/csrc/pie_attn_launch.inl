@@ -18,6 +18,10 @@ cudaError_t launch_decode_attn(uint16_t* out, const uint16_t* q, const uint16_t*
                                const KvLayout& kv, const int32_t* pos, int B, int Hq, int Hkv, int D,
                                float scale, int nsplit, float* ws, cudaStream_t st) {
   if (B == 0) return cudaSuccess;
+  // tensor-core kernel (pie_fa.cu) unless PIE_DECODE_ATTN=simt; it takes the n_rep query heads of a kv head as MMA rows
+  static const bool simt = [] { const char* e = getenv("PIE_DECODE_ATTN"); return e && e[0] == 's'; }();
+  if (!simt && Hq / Hkv <= 16 && nsplit <= 32)
+    return launch_decode_attn_tc(out, q, kc, vc, kv, pos, B, Hq, Hkv, D, scale, nsplit, ws, st);
   DecAttnArgs a;
   a.out = out; a.q = q; a.kc = kc; a.vc = vc; a.kv = kv; a.pos = pos;
   a.Hq = Hq; a.Hkv = Hkv; a.nsplit = nsplit; a.rg = 1;

@@ -16,7 +16,7 @@
 
 namespace pie {
 
-constexpr int kFaBQ = 64, kFaBKV = 64, kFaThreads = 128;
+constexpr int kFaBQ = 64, kFaBKV = 64, kFaThreads = 128, kFaMaxSplits = 32;
 
 __device__ __forceinline__ size_t fa_kv_addr(const KvLayout& kv, int b, int h, int t) {
   if (kv.page_table) {
@@ -183,6 +183,222 @@ __global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_con
     if (r0 < a.L) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * a.Hq * D + d) = pack_bf16(o[i][0] * i0, o[i][1] * i0);
     if (r1 < a.L) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * a.Hq * D + d) = pack_bf16(o[i][2] * i1, o[i][3] * i1);
   }
+}
+
+// ---- decode attention (L = 1) for batched / long-context steps: the n_rep query heads of a kv head are the M rows ------
+// Same operand path as the prefill kernel; the 4 warps of a CTA share each 64-key stage and take 16 keys of it each,
+// every warp with its own running (max, sum, O) that a shared-memory pass merges at the end.  grid = (splits of the
+// context, kv heads, sequences); split partials go through the same workspace records and last-arriver merge as
+// decode_attn_kernel ([B * Hq][nsplit][D + 2] floats + one counter per (sequence, kv head)).  K / V bytes are read
+// once per kv head (the SIMT kernel reads them once per pair of query heads) and the dot products leave the FMA pipe.
+struct FaDecArgs {
+  uint16_t* out;
+  const uint16_t* q;     // [B, Hq, D], rope applied
+  const uint16_t* kc;
+  const uint16_t* vc;
+  KvLayout kv;
+  const int32_t* pos;    // keys 0 .. pos[b] are attended
+  int Hq, Hkv, nsplit;
+  float scale_log2e;
+  float* ws_part;
+  unsigned int* ws_cnt;
+};
+
+template <int D>
+__global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_constant__ FaDecArgs a) {
+  constexpr int KC = D / 16, DT = D / 8, CPR = D / 8, TILE = kFaBKV * D * 2, PW = D + 2;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_last;
+  __shared__ float s_m[16][kFaMaxSplits], s_l[16][kFaMaxSplits], s_w[16][kFaMaxSplits];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t4 = lane & 3;
+  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int n_rep = a.Hq / a.Hkv, qh0 = kvh * n_rep;
+  const int p = a.pos[b], ctx = p + 1;
+  const int tiles = (ctx + kFaBKV - 1) / kFaBKV, per = (tiles + a.nsplit - 1) / a.nsplit;
+  const int j0 = split * per, j1 = min(tiles, j0 + per);
+  const uint32_t sK = smem_u32(smem), sV = sK + 2 * TILE;
+
+  auto issue = [&](int j) {
+    const uint32_t dk = sK + ((j - j0) & 1) * TILE, dv = sV + ((j - j0) & 1) * TILE;
+    for (int i = tid; i < kFaBKV * CPR; i += kFaThreads) {
+      const int r = i / CPR, c = i % CPR;
+      const int t = min(j * kFaBKV + r, p);
+      const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
+      cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
+      cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+    }
+    cp_async_commit();
+  };
+  if (j0 < j1) issue(j0);
+
+  // Q fragments: row g = query head qh0 + g (rows >= n_rep are zero)
+  uint32_t qf[KC][4];
+  {
+    const uint32_t* q0 = reinterpret_cast<const uint32_t*>(a.q + ((size_t)b * a.Hq + qh0 + min(g, n_rep - 1)) * D);
+    const uint32_t* q1 = reinterpret_cast<const uint32_t*>(a.q + ((size_t)b * a.Hq + qh0 + min(g + 8, n_rep - 1)) * D);
+    const bool v0 = g < n_rep, v1 = g + 8 < n_rep;
+#pragma unroll
+    for (int kc = 0; kc < KC; ++kc) {
+      qf[kc][0] = v0 ? ldcg32(q0 + kc * 8 + t4) : 0u;
+      qf[kc][1] = v1 ? ldcg32(q1 + kc * 8 + t4) : 0u;
+      qf[kc][2] = v0 ? ldcg32(q0 + kc * 8 + 4 + t4) : 0u;
+      qf[kc][3] = v1 ? ldcg32(q1 + kc * 8 + 4 + t4) : 0u;
+    }
+  }
+  float o[DT][4];
+#pragma unroll
+  for (int i = 0; i < DT; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  for (int j = j0; j < j1; ++j) {
+    if (j + 1 < j1) { issue(j + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const uint32_t tk = sK + ((j - j0) & 1) * TILE, tv = sV + ((j - j0) & 1) * TILE;
+    float s[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      s[n][0] = s[n][1] = s[n][2] = s[n][3] = 0.f;
+#pragma unroll
+      for (int kc = 0; kc < KC; kc += 2) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(tk + fa_tile_off<D>(warp * 16 + n * 8 + (lane & 7), kc * 2 + (lane >> 3)), b0, b1, b2, b3);
+        mma_bf16_16816(s[n], qf[kc][0], qf[kc][1], qf[kc][2], qf[kc][3], b0, b1);
+        mma_bf16_16816(s[n], qf[kc + 1][0], qf[kc + 1][1], qf[kc + 1][2], qf[kc + 1][3], b2, b3);
+      }
+    }
+    const int key0 = j * kFaBKV + warp * 16 + 2 * t4;
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s[n][e] *= a.scale_log2e;
+      const int k = key0 + n * 8;
+      if (k > p) { s[n][0] = -INFINITY; s[n][2] = -INFINITY; }
+      if (k + 1 > p) { s[n][1] = -INFINITY; s[n][3] = -INFINITY; }
+      mx0 = fmaxf(mx0, fmaxf(s[n][0], s[n][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[n][2], s[n][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float c0 = mn0 == -INFINITY ? 1.f : exp2f(m0 - mn0), c1 = mn1 == -INFINITY ? 1.f : exp2f(m1 - mn1);
+    const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
+    const float p00 = exp2f(s[0][0] - ms0), p01 = exp2f(s[0][1] - ms0), p02 = exp2f(s[0][2] - ms1), p03 = exp2f(s[0][3] - ms1);
+    const float p10 = exp2f(s[1][0] - ms0), p11 = exp2f(s[1][1] - ms0), p12 = exp2f(s[1][2] - ms1), p13 = exp2f(s[1][3] - ms1);
+    l0 = l0 * c0 + (p00 + p01 + p10 + p11);
+    l1 = l1 * c1 + (p02 + p03 + p12 + p13);
+    m0 = mn0; m1 = mn1;
+    const uint32_t a0 = pack_bf16(p00, p01), a1 = pack_bf16(p02, p03), a2 = pack_bf16(p10, p11), a3 = pack_bf16(p12, p13);
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+#pragma unroll
+    for (int dj = 0; dj < DT; dj += 2) {
+      uint32_t b0, b1, b2, b3;
+      ldsm_x4_trans(tv + fa_tile_off<D>(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, dj + (lane >> 4)), b0, b1, b2, b3);
+      mma_bf16_16816(o[dj], a0, a1, a2, a3, b0, b1);
+      mma_bf16_16816(o[dj + 1], a0, a1, a2, a3, b2, b3);
+    }
+    __syncthreads();
+  }
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  // per-warp partials -> shared memory (the stages are free: the loop ended with a barrier), rows < n_rep only
+  float* rec = reinterpret_cast<float*>(smem);  // [4 warps][n_rep][PW]
+  if (g < n_rep) {
+    float* r0 = rec + ((size_t)warp * n_rep + g) * PW;
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { r0[i * 8 + 2 * t4] = o[i][0]; r0[i * 8 + 2 * t4 + 1] = o[i][1]; }
+    if (t4 == 0) { r0[D] = m0; r0[D + 1] = l0; }
+  }
+  if (g + 8 < n_rep) {
+    float* r1 = rec + ((size_t)warp * n_rep + g + 8) * PW;
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { r1[i * 8 + 2 * t4] = o[i][2]; r1[i * 8 + 2 * t4 + 1] = o[i][3]; }
+    if (t4 == 0) { r1[D] = m1; r1[D + 1] = l1; }
+  }
+  __syncthreads();
+  const size_t rec0 = ((size_t)b * a.Hq + qh0) * a.nsplit;
+  for (int i = tid; i < n_rep * D; i += kFaThreads) {
+    const int r = i / D, d = i % D;
+    float mn = -INFINITY;
+    for (int w = 0; w < 4; ++w) mn = fmaxf(mn, rec[((size_t)w * n_rep + r) * PW + D]);
+    float lt = 0.f, at = 0.f;
+    for (int w = 0; w < 4; ++w) {
+      const float* rw = rec + ((size_t)w * n_rep + r) * PW;
+      const float cw = rw[D] == -INFINITY ? 0.f : exp2f(rw[D] - mn);
+      lt += rw[D + 1] * cw;
+      at += rw[d] * cw;
+    }
+    if (a.nsplit == 1) {
+      a.out[((size_t)b * a.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+    } else {
+      float* pr = a.ws_part + (rec0 + (size_t)r * a.nsplit + split) * PW;
+      pr[d] = at;
+      if (d == 0) { pr[D] = mn; pr[D + 1] = lt; }
+    }
+  }
+  if (a.nsplit == 1) return;
+  __threadfence();
+  __syncthreads();
+  const int cidx = b * a.Hkv + kvh;
+  if (tid == 0) s_last = (atomicAdd(&a.ws_cnt[cidx], 1u) == (unsigned)a.nsplit - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // merge of the splits: (max, sum) of every record first (one parallel round trip), then the weighted rows with the
+  // loads of 8 splits in flight per thread
+  for (int i = tid; i < n_rep * a.nsplit; i += kFaThreads) {
+    const int r = i / a.nsplit, sp = i % a.nsplit;
+    const float* pr = a.ws_part + (rec0 + (size_t)r * a.nsplit + sp) * PW;
+    s_m[r][sp] = ldcg_f32(pr + D);
+    s_l[r][sp] = ldcg_f32(pr + D + 1);
+  }
+  __syncthreads();
+  for (int i = tid; i < n_rep * a.nsplit; i += kFaThreads) {
+    const int r = i / a.nsplit, sp = i % a.nsplit;
+    float mn = -INFINITY;
+    for (int k = 0; k < a.nsplit; ++k) mn = fmaxf(mn, s_m[r][k]);
+    s_w[r][sp] = s_m[r][sp] == -INFINITY ? 0.f : exp2f(s_m[r][sp] - mn);
+  }
+  __syncthreads();
+  for (int i = tid; i < n_rep * D; i += kFaThreads) {
+    const int r = i / D, d = i % D;
+    const float* pr = a.ws_part + (rec0 + (size_t)r * a.nsplit) * PW + d;
+    float lt = 0.f, at = 0.f;
+#pragma unroll 8
+    for (int sp = 0; sp < a.nsplit; ++sp) {  // split order: deterministic
+      lt += s_l[r][sp] * s_w[r][sp];
+      at += ldcg_f32(pr + (size_t)sp * PW) * s_w[r][sp];
+    }
+    a.out[((size_t)b * a.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+  }
+  if (tid == 0) a.ws_cnt[cidx] = 0;
+}
+
+cudaError_t launch_decode_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
+                                  const KvLayout& kv, const int32_t* pos, int B, int Hq, int Hkv, int D, float scale,
+                                  int nsplit, float* ws, cudaStream_t st) {
+  if (nsplit > kFaMaxSplits) return cudaErrorInvalidValue;
+  FaDecArgs a;
+  a.out = out; a.q = q; a.kc = kc; a.vc = vc; a.kv = kv; a.pos = pos; a.Hq = Hq; a.Hkv = Hkv; a.nsplit = nsplit;
+  a.scale_log2e = scale * 1.4426950408889634f;
+  const size_t cnt_bytes = (((size_t)B * Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
+  a.ws_cnt = reinterpret_cast<unsigned int*>(ws);
+  a.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + cnt_bytes);
+  const size_t smem = (size_t)4 * kFaBKV * D * 2;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(fa_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kFaBKV * 128 * 2);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  const dim3 grid(nsplit, Hkv, B);
+  count_launch();
+  if (D == 128) fa_decode_kernel<128><<<grid, kFaThreads, smem, st>>>(a);
+  else fa_decode_kernel<64><<<grid, kFaThreads, smem, st>>>(a);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_prefill_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,

@@ -89,6 +89,9 @@ cudaError_t launch_kv_write(uint16_t* kc, uint16_t* vc, const KvLayout& kv, cons
 cudaError_t launch_decode_attn(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
                                const KvLayout& kv, const int32_t* pos, int B, int Hq, int Hkv, int D,
                                float scale, int nsplit, float* ws, cudaStream_t st);
+cudaError_t launch_decode_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
+                                  const KvLayout& kv, const int32_t* pos, int B, int Hq, int Hkv, int D, float scale,
+                                  int nsplit, float* ws, cudaStream_t st);
 cudaError_t launch_prefill_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,
                                    const KvLayout& kv, int B, int Hq, int Hkv, int L, int D, int offset, float scale,
                                    cudaStream_t st);

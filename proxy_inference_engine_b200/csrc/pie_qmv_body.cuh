@@ -40,48 +40,86 @@ __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* 
   const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31;
   const int xrow = qmv_xrow_bytes(a.kslice);
   // fused RMSNorm (mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111): inverse rms over the FULL row
-  float inv[8 * MT];
+  // M <= 2: every thread takes part in each row (one round trip per row).  More rows: a warp per row with 8 loads in
+  // flight per lane, all rows concurrently, ONE barrier.  The inverse rms values end up in red[0 .. M).
   if (a.norm_w) {
-    for (int m = 0; m < a.M; ++m) {
-      float ss = 0.f;
-      const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld);
-      for (int i = tid; i < a.K / 8; i += nthr) {
-        uint4 v = ldcg128(xr + i);
-        uint32_t u[4] = {v.x, v.y, v.z, v.w};
+    if (a.M <= 2) {
+      float inv2[2] = {0.f, 0.f};
+      for (int m = 0; m < a.M; ++m) {
+        float ss = 0.f;
+        const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld);
+        for (int i = tid; i < a.K / 8; i += nthr) {
+          uint4 v = ldcg128(xr + i);
+          uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { float lo = bf16lo(u[j]), hi = bf16hi(u[j]); ss += lo * lo + hi * hi; }
+          for (int j = 0; j < 4; ++j) { float lo = bf16lo(u[j]), hi = bf16hi(u[j]); ss += lo * lo + hi * hi; }
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) red[tid >> 5] = ss;
+        __syncthreads();
+        float tot = 0.f;
+        for (int w = 0; w < (nthr >> 5); ++w) tot += red[w];
+        inv2[m] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
+        __syncthreads();
       }
-      ss = warp_sum(ss);
-      if (lane == 0) red[tid >> 5] = ss;
-      __syncthreads();
-      float tot = 0.f;
-      for (int w = 0; w < (nthr >> 5); ++w) tot += red[w];
-      inv[m] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
-      __syncthreads();
+      if (tid < a.M) red[tid] = inv2[tid];
+    } else {
+      const int nch = a.K / 8;
+      for (int m = tid >> 5; m < a.M; m += nthr >> 5) {
+        float ss = 0.f;
+        const uint4* xr = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld);
+        for (int i0 = lane; i0 < nch; i0 += 256) {
+          uint4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = i0 + 32 * u < nch ? ldcg128(xr + i0 + 32 * u) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t w4[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { float lo = bf16lo(w4[j]), hi = bf16hi(w4[j]); ss += lo * lo + hi * hi; }
+          }
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) red[m] = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+      }
     }
+    __syncthreads();
   }
   const int bpr = klen / 16;             // 16-element blocks per row in this slice (multiple of 4)
   const int total = a.M * bpr;
   const int rounds = (total + nthr - 1) / nthr;
-  for (int it = 0; it < rounds; ++it) {
+  for (int it0 = 0; it0 < rounds; it0 += 4) {
+   uint4 pre[4][2];  // the loads of four rounds are requested before the first is used
+#pragma unroll
+   for (int u = 0; u < 4; ++u) {
+     const int idx = (it0 + u) * nthr + tid;
+     if (idx < total) {
+       const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)(idx / bpr) * a.x_ld + k0 + (idx % bpr) * 16);
+       pre[u][0] = ldcg128(src); pre[u][1] = ldcg128(src + 1);
+     }
+   }
+#pragma unroll
+   for (int u = 0; u < 4; ++u) {
+    const int it = it0 + u;
+    if (it >= rounds) break;
     const int idx = it * nthr + tid;
     const bool ok = idx < total;
     const int m = ok ? idx / bpr : 0, blk = ok ? idx % bpr : 0;
     float v[16];
     if (ok) {
-      const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld + k0 + blk * 16);
-      uint4 p0 = ldcg128(src), p1 = ldcg128(src + 1);
-      uint32_t u[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+      const uint4 p0 = pre[u][0], p1 = pre[u][1];
+      uint32_t u8[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(u[j]); v[2 * j + 1] = bf16hi(u[j]); }
+      for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(u8[j]); v[2 * j + 1] = bf16hi(u8[j]); }
       if (a.norm_w) {
         const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + k0 + blk * 16);
         uint4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
         uint32_t wu[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        const float inv_m = red[m];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          v[2 * j] = bfround(bfround(v[2 * j] * inv[m]) * bf16lo(wu[j]));
-          v[2 * j + 1] = bfround(bfround(v[2 * j + 1] * inv[m]) * bf16hi(wu[j]));
+          v[2 * j] = bfround(bfround(v[2 * j] * inv_m) * bf16lo(wu[j]));
+          v[2 * j + 1] = bfround(bfround(v[2 * j + 1] * inv_m) * bf16hi(wu[j]));
         }
       }
     } else {
@@ -110,6 +148,7 @@ __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* 
       dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
       if ((blk & 3) == 0) sumx[((blk >> 2) * MT + (m >> 3)) * 8 + (m & 7)] = s;
     }
+   }
   }
 }
 

@@ -40,7 +40,7 @@ def _segs(*linears):
 class DecodeEngine:
     def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
                  use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2,
-                 fused: bool = False, trace: bool = False, attn_fused: bool = True, tp=None):
+                 fused: bool = False, trace: bool = False, attn_fused: bool | None = None, tp=None):
         a = model.args
         self.model, self.args, self.B, self.max_context = model, a, batch, max_context
         self.pdl, self.use_graph = int(pdl), use_graph
@@ -92,8 +92,12 @@ class DecodeEngine:
         L = _lib.load()
         self.L = L
         self.nsplit = L.pie_decode_attn_pick_splits(B, self.Hq, self.Hkv, max_context)
-        # rope + KV append + flash-decode in one launch (pie_decode_attn_fused) unless asked for the three-operator form
-        self.attn_fused = attn_fused
+        # Two forms of decode attention.  Latency form: rope + KV append + SIMT flash-decode in ONE launch
+        # (pie_decode_attn_fused).  Throughput form: pie_rope_kv_append + the tensor-core kernel of pie_fa.cu, which
+        # reads K/V once per kv head.  Measured per layer on B200 (tools/run_attn_compare.sh; 8B shapes, us):
+        #   bs1 ctx500 10.8 / 12.9, bs1 ctx2048 16.9 / 17.4, bs1 ctx8000 40.5 / 22.2, bs4 ctx2048 32.6 / 23.1,
+        #   bs32 ctx2048 203 / 77  ->  the latency form while batch x context stays within 4096 keys.
+        self.attn_fused = (batch * max_context <= 4096) if attn_fused is None else attn_fused
         # the splits of a unit form one thread-block cluster and merge through distributed shared memory; measured on
         # B200 (8B, bs1): 3..6 splits cost the same, clusters of 8 are markedly slower to schedule -> cap at 6
         self.nsplit_fused = min(6, L.pie_decode_step_pick_splits(B, self.Hq, self.Hkv, max_context))

@@ -82,7 +82,7 @@ def test_fused_step_matches_per_operator_path(bits, head_dim, batch, heads, kv_h
     assert torch.equal(ta, tb)
     n = ctx + 5
     assert torch.equal(ca[-1].keys[:, :, :n], cb[-1].keys[:, :, :n]) or \
-        rel_l2(cb[-1].keys[:, :, :n].float().cpu().numpy(), ca[-1].keys[:, :, :n].float().cpu().numpy()) < 2e-3
+        rel_l2(cb[-1].keys[:, :, :n].float().cpu().numpy(), ca[-1].keys[:, :, :n].float().cpu().numpy()) < 5e-3
 
 
 def test_decode_engine_is_deterministic_and_free_running():
