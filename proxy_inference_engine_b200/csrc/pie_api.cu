@@ -124,6 +124,21 @@ int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x,
   return PIE_OK;
 }
 int status_of(cudaError_t e) { return cuda_status(e); }
+
+// Workspace of the batched-decode GEMM, laid out so that it can share the buffer with the GEMV: the counter region
+// comes first and is as large as the GEMV's (both kernels leave their counters zero), then the normalised
+// activations, then the split-K partials.
+static inline size_t qmd_cnt_bytes(long long rows_total) { return ((size_t)(rows_total / 8 + 16) * 4 + 255) & ~(size_t)255; }
+static size_t qmd_total_bytes(int M, long long rows_total, int K, int dual, int bits) {
+  const int mb = M > kMaxBatch ? kMaxBatch : M;
+  size_t worst = 0;
+  const int t0 = (int)((rows_total + 127) / 128);
+  for (int t = t0; t <= t0 + kMaxSeg; ++t) {
+    const size_t b = qmd_ws_bytes(mb, t, K, qmd_pick_ksplit(t, K, dual, bits), true);
+    if (b > worst) worst = b;
+  }
+  return qmd_cnt_bytes(rows_total) + worst;
+}
 }  // namespace pie
 
 using namespace pie;
@@ -172,7 +187,12 @@ size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int du
   if (M <= 0 || n_total <= 0 || K <= 0 || (bits != 4 && bits != 8) || K % stage_k(bits) != 0) return 0;
   QmvPlan p = plan_qmv(M > kMaxBatch ? kMaxBatch : M, n_total, K, bits, dual, ksplit_hint, 0);
   p.ntiles += kMaxSeg;  // segments are tiled separately: up to one ragged tile each
-  return qmv_ws_bytes(p);
+  size_t need = qmv_ws_bytes(p);
+  if (M > 8 && K % 128 == 0) {
+    const size_t q = qmd_total_bytes(M, n_total, K, dual, bits);
+    if (q > need) need = q;
+  }
+  return need;
 }
 
 int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
@@ -186,6 +206,36 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
     const int st0 = build_qmv_args(a, p, out, out_ld, x, x_ld, m0, mb, K, segs, nseg, group_size, bits, norm_weight, eps,
                                    epilogue, residual, ksplit_hint, workspace, workspace_bytes, 0);
     if (st0 != PIE_OK) return st0;
+    // Batched-decode GEMM on tcgen05 (pie_qmd.cu).  PIE_QMD: 0 never, 1 where it measured faster than the GEMV at 32
+    // rows (B200, 8B shapes, us GEMV / tcgen05: q8 gate+up 121 / 98, q8 head 417 / 290, q4 head 233 / 217; the narrow
+    // matrices and 4-bit gate+up / down are still faster on the GEMV: DESIGN.md section 4.6), 2 wherever it is supported.
+    const int qmd_mode = env_int("PIE_QMD", 1);  // read per call: the tests switch it
+    long long rows_total = 0;
+    int nt = 0;
+    for (int i = 0; i < nseg; ++i) { rows_total += segs[i].N; nt += (segs[i].N + 127) / 128; }
+    if (a.dual) { rows_total = 2LL * segs[0].N; nt = (segs[0].N + 127) / 128; }
+    const bool qmd_pays = mb > 16 && ((bits == 8 && rows_total >= 16384) || rows_total >= 65536);
+    if (qmd_mode && (qmd_mode == 2 || qmd_pays) && qmd_supported(mb, K, x_ld, group_size, bits) &&
+        (!norm_weight || x_ld == K)) {
+      if (a.dual) rows_total = segs[0].N;
+      const int ks = qmd_pick_ksplit(nt, K, a.dual, bits);
+      const size_t cnt = qmd_cnt_bytes(rows_total), xn_bytes = norm_weight ? (((size_t)mb * K * 2 + 255) & ~(size_t)255) : 0;
+      if (workspace && cnt + qmd_ws_bytes(mb, nt, K, ks, norm_weight != nullptr) <= workspace_bytes) {
+        uint8_t* wsb = (uint8_t*)workspace;
+        const uint16_t* xin = a.x;
+        int xin_ld = x_ld;
+        if (norm_weight) {
+          const int st1 = cuda_status(launch_rms_norm((uint16_t*)(wsb + cnt), a.x, a.norm_w, mb, K, eps, (cudaStream_t)stream));
+          if (st1 != PIE_OK) return st1;
+          xin = (const uint16_t*)(wsb + cnt);
+          xin_ld = K;
+        }
+        float* part = (float*)(wsb + cnt + xn_bytes + (((size_t)nt * 16 + 255) & ~(size_t)255));
+        const int st2 = cuda_status(launch_qmd(a, xin, xin_ld, bits, part, (unsigned int*)workspace, ks, (cudaStream_t)stream));
+        if (st2 != PIE_OK) return st2;
+        continue;
+      }
+    }
     const int st = cuda_status(launch_qmv(a, bits, p.warps, p.grid, pdl != 0, (cudaStream_t)stream));
     if (st != PIE_OK) return st;
   }

@@ -290,7 +290,12 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
     l0 = l0 * c0 + (p00 + p01 + p10 + p11);
     l1 = l1 * c1 + (p02 + p03 + p12 + p13);
     m0 = mn0; m1 = mn1;
+    // P as a bf16 pair (hi + lo): 16 significant bits, so this kernel agrees with the fp32-probability SIMT kernel to
+    // ~1e-4 and greedy tokens do not depend on which of the two the engine picked; the extra 16 MMAs ride under the
+    // K/V stream (the kernel is HBM-bound)
     const uint32_t a0 = pack_bf16(p00, p01), a1 = pack_bf16(p02, p03), a2 = pack_bf16(p10, p11), a3 = pack_bf16(p12, p13);
+    const uint32_t e0 = pack_bf16(p00 - bf16lo(a0), p01 - bf16hi(a0)), e1 = pack_bf16(p02 - bf16lo(a1), p03 - bf16hi(a1));
+    const uint32_t e2 = pack_bf16(p10 - bf16lo(a2), p11 - bf16hi(a2)), e3 = pack_bf16(p12 - bf16lo(a3), p13 - bf16hi(a3));
 #pragma unroll
     for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
 #pragma unroll
@@ -299,6 +304,8 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
       ldsm_x4_trans(tv + fa_tile_off<D>(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, dj + (lane >> 4)), b0, b1, b2, b3);
       mma_bf16_16816(o[dj], a0, a1, a2, a3, b0, b1);
       mma_bf16_16816(o[dj + 1], a0, a1, a2, a3, b2, b3);
+      mma_bf16_16816(o[dj], e0, e1, e2, e3, b0, b1);
+      mma_bf16_16816(o[dj + 1], e0, e1, e2, e3, b2, b3);
     }
     __syncthreads();
   }

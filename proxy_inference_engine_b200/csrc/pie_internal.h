@@ -68,6 +68,12 @@ cudaError_t launch_qmv_generic(uint16_t* y, const uint16_t* x, const uint32_t* w
 size_t qmv_smem_bytes(int M, int kslice, int bits, int warps, int mt);
 cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, const uint16_t* s, const uint16_t* b,
                           int M, int N, int K, int bits, cudaStream_t st);
+// batched-decode GEMM on tcgen05 (pie_qmd.cu): 9 .. 32 activation rows per pass
+int qmd_pick_ksplit(int ntiles, int K, int dual, int bits);
+size_t qmd_ws_bytes(int M, int ntiles, int K, int ksplit, bool norm);
+bool qmd_supported(int mb, int K, int x_ld, int group_size, int bits);
+cudaError_t launch_qmd(const QmvArgs& g, const uint16_t* x, int x_ld, int bits, float* ws_part, unsigned int* ws_cnt,
+                       int ksplit, cudaStream_t st);
 int qmv_mt(int M);
 int num_sms();
 

@@ -159,12 +159,21 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 // ------------------------------------------------------------------ bf16 helpers
 __device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
-__device__ __forceinline__ uint16_t f2bf(float f) {
-  return __bfloat16_as_ushort(__float2bfloat16_rn(f));  // RNE; NaN -> 0x7FFF canonical
-}
-__device__ __forceinline__ float bfround(float f) { return __uint_as_float(((uint32_t)f2bf(f)) << 16); }
+// fp32 -> bf16, round to nearest even, NaN -> 0x7FFF canonical.  Always through the PACKED conversion
+// (F2FP.BF16.F32.PACK_AB, full-rate ALU pipe): the scalar F2F.BF16.F32 issues on the quarter-rate XU pipe and was the top
+// stall in the dequantising producers.
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
-  return (uint32_t)f2bf(lo) | ((uint32_t)f2bf(hi) << 16);
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ uint16_t f2bf(float f) { return (uint16_t)(pack_bf16(f, 0.f) & 0xffffu); }
+__device__ __forceinline__ float bfround(float f) { return __uint_as_float(pack_bf16(0.f, f) & 0xffff0000u); }
+// bf16x2 fused multiply-add (HFMA2.BF16, FMA pipe): fp32-exact product and sum, ONE rounding per lane
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

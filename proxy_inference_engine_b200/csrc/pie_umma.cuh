@@ -1,0 +1,60 @@
+// tcgen05 / TMEM helpers shared by the prefill GEMM (pie_qmm.cu) and the batched-decode GEMM (pie_qmd.cu).
+#pragma once
+#include "pie_ptx.cuh"
+
+namespace pie {
+
+// shared-memory matrix descriptor: K-major, 128-byte swizzle, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor)
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);  // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                        // leading byte offset: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset between 8-row groups
+  d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, A = B = bf16, both K-major, M 128, N `n`
+constexpr uint32_t umma_idesc_bf16_m128(int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc),
+      "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+      "%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// The BITS-wide field of `w` at bit `pos` lifted into an fp32 mantissa: 128 + q (4-bit) or 256 + q (8-bit), exactly,
+// with one shift and one LOP3 -- no integer-to-float conversion (those run on the 16-lane XU pipe).  The offset is
+// folded into the bias: w_hat = (off + q) * s + (b - off * s); the fold costs |off * s| * 2^-24, far below the
+// bf16 rounding of w_hat.
+template <int BITS>
+__device__ __forceinline__ float lift_f32(uint32_t w, int pos) {
+  constexpr int LSB = BITS == 4 ? 16 : 15;             // mantissa bit that weighs 1 at exponent 2^7 / 2^8
+  constexpr uint32_t MASK = ((1u << BITS) - 1u) << LSB;
+  constexpr uint32_t MAGIC = BITS == 4 ? 0x43000000u : 0x43800000u;
+  const uint32_t v = pos <= LSB ? (w << (LSB - pos)) : (w >> (pos - LSB));
+  return __uint_as_float((v & MASK) | MAGIC);
+}
+
+}  // namespace pie

@@ -146,6 +146,46 @@ def test_fused_norm_qkv_resadd_swiglu(env, bits, M, ksplit):
     assert rel_l2(t2n(res), ref_h) < 3e-3
 
 
+@pytest.mark.parametrize("bits", [4, 8])
+@pytest.mark.parametrize("M", [9, 16, 32, 40])
+def test_batched_decode_gemm_tcgen05(env, bits, M, monkeypatch):
+    """9..32 rows per pass can go to the tcgen05 batched-decode GEMM (pie_qmd.cu): weights rounded once to bf16 like Metal
+    qmm_t (kernels/quantized.h:954-1078).  Same sub-block as above, ragged N (320 rows: a partial 128-row tile), split-K
+    for the narrow matrices, and M = 40 = one tcgen05 pass + one GEMV pass on the SAME workspace."""
+    orc, ops = env
+    monkeypatch.setenv("PIE_QMD", "2")  # everywhere it is supported (default: only where it measured faster)
+    rng = np.random.default_rng(100 + bits + M)
+    h, f, nq, nkv = 1024, 2048, 320, 128
+    mk = lambda n, k: orc.quantize((rng.uniform(-1, 1, (n, k)) / np.sqrt(k)).astype(np.float32), 64, bits)
+    up = lambda t: (n2t_words(t[0]), n2t_bf16(t[1]), n2t_bf16(t[2]))
+    Wq, Wk, Wv, Wg, Wu, Wd = mk(nq, h), mk(nkv, h), mk(nkv, h), mk(f, h), mk(f, h), mk(h, f)
+    x = orc.round_bf16(rng.standard_normal((M, h)).astype(np.float32) * 2)
+    nw = orc.round_bf16(1 + 0.1 * rng.standard_normal(h).astype(np.float32))
+    xn = orc.rms_norm(x, nw, 1e-5, "B")
+
+    def qm(a, W):  # bf16(weights), fp64 accumulate, one rounding
+        w = orc.round_bf16(orc.dequantize(W[0], W[1], W[2], 64, bits, t_bf16=False)).astype(np.float64)
+        return orc.round_bf16((a.astype(np.float64) @ w.T).astype(np.float32))
+
+    out = torch.empty((M, nq + 2 * nkv), dtype=torch.bfloat16, device="cuda")
+    _fused(ops, out, n2t_bf16(x), [up(Wq), up(Wk), up(Wv)], M, h, bits, n2t_bf16(nw), 0, None)
+    ref = np.concatenate([qm(xn, Wq), qm(xn, Wk), qm(xn, Wv)], axis=1)
+    assert rel_l2(t2n(out), ref) < 3e-3, rel_l2(t2n(out), ref)
+    act = torch.empty((M, f), dtype=torch.bfloat16, device="cuda")
+    _fused(ops, act, n2t_bf16(x), [up(Wg), up(Wu)], M, h, bits, n2t_bf16(nw), 2, None)
+    ref_act = orc.silu_mul(qm(xn, Wg), qm(xn, Wu), "B")
+    assert rel_l2(t2n(act), ref_act) < 6e-3, rel_l2(t2n(act), ref_act)
+    res = n2t_bf16(x).clone()
+    _fused(ops, res, n2t_bf16(ref_act), [up(Wd)], M, f, bits, None, 1, res)
+    ref_h = orc.add(x, qm(ref_act, Wd), "B")
+    assert rel_l2(t2n(res), ref_h) < 3e-3, rel_l2(t2n(res), ref_h)
+    # plain operator form, and agreement with the GEMV (fp32 weights) within the bf16 rounding of the weights
+    y = t2n(ops.quantized_matmul(n2t_bf16(x), *up(Wg), True, 64, bits))
+    assert rel_l2(y, qm(x, Wg)) < 3e-3
+    y8 = t2n(ops.quantized_matmul(n2t_bf16(x[:8]), *up(Wg), True, 64, bits))
+    assert rel_l2(y[:8], y8) < 6e-3
+
+
 def test_argmax_first_index_and_advance(env):
     orc, ops = env
     lg = torch.zeros((3, 1000), dtype=torch.bfloat16, device="cuda")

@@ -77,12 +77,31 @@ def test_fused_step_matches_per_operator_path(bits, head_dim, batch, heads, kv_h
             lg.append(eng.logits.float().clone())
         outs.append((eng.generated(), torch.stack(lg), eng.cache))
     (ta, la, ca), (tb, lb, cb), (tc, lc, cc) = outs   # three-operator attention / one launch per step / fused attention
-    assert rel_l2(lc.cpu().numpy(), la.cpu().numpy()) < 1e-2 and torch.equal(ta, tc)
-    assert rel_l2(lb.cpu().numpy(), la.cpu().numpy()) < 1e-2   # bf16 ulp is 4e-3: a few logits round differently
-    assert torch.equal(ta, tb)
-    n = ctx + 5
-    assert torch.equal(ca[-1].keys[:, :, :n], cb[-1].keys[:, :, :n]) or \
-        rel_l2(cb[-1].keys[:, :, :n].float().cpu().numpy(), ca[-1].keys[:, :, :n].float().cpu().numpy()) < 5e-3
+
+    def same_until_near_tie(t_ref, l_ref, t_got, l_got):
+        """The three-operator form runs the tensor-core attention kernel, whose fp32 summation order differs from the
+        SIMT kernel inside the fused forms: logits agree to bf16 rounding noise, and on a random-init model a greedy
+        token may flip at a near-tie.  Rows are compared up to their first differing token, which must BE a near-tie."""
+        off = t_ref.shape[1] - l_ref.shape[0]  # tokens sampled before the first timed step (the prefill's token)
+        for b in range(t_ref.shape[0]):
+            n = t_ref.shape[1]
+            diff = (t_ref[b] != t_got[b]).nonzero()
+            first = int(diff[0]) if len(diff) else n
+            assert first >= off  # the prefill is common to all engines
+            if first < n:  # token `first` was sampled from the logits of step `first - off`
+                lr = l_ref[first - off, b]
+                gap = abs(float(lr[int(t_ref[b, first])] - lr[int(t_got[b, first])]))
+                assert gap <= 2e-2 * float(lr.abs().max()), (b, first, gap)
+            k = min(first - off + 1, l_ref.shape[0])  # steps whose input tokens were still identical
+            assert rel_l2(l_got[:k, b].cpu().numpy(), l_ref[:k, b].cpu().numpy()) < 1e-2
+
+    same_until_near_tie(ta, la, tc, lc)
+    same_until_near_tie(ta, la, tb, lb)
+    assert torch.equal(tb, tc)   # the two fused forms share the attention arithmetic: identical tokens
+    if torch.equal(ta, tb):
+        n = ctx + 5
+        assert torch.equal(ca[-1].keys[:, :, :n], cb[-1].keys[:, :, :n]) or \
+            rel_l2(cb[-1].keys[:, :, :n].float().cpu().numpy(), ca[-1].keys[:, :, :n].float().cpu().numpy()) < 5e-3
 
 
 def test_decode_engine_is_deterministic_and_free_running():
