@@ -189,6 +189,27 @@ def time_qmv_launches(eng, n_steps=3):
     return ms * 1e-3, per_step
 
 
+def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the GEMV per launch, from the committed `ncu --set full` capture
+    (profiles/r01e_prof_qmv_ncu_full_summary.csv: the q4 gate+up, down, qkv and o launches of one 8B layer).  The capture
+    holds four of the five shapes, so the measured traffic / algorithmic ratio of those launches scales this run's
+    average launch.  None if the capture is absent or was taken at another bit width."""
+    import csv
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01e_prof_qmv_ncu_full_summary.csv")
+    if bits != 4 or not os.path.exists(path):
+        return None, "no ncu capture for this configuration"
+    rows = {r[0]: r for r in csv.reader(open(path)) if r}
+    unit = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}
+    try:
+        rd = sum(float(x) for x in rows["dram__bytes_read.sum"][2:6]) * unit[rows["dram__bytes_read.sum"][1]]
+        wr = sum(float(x) for x in rows["dram__bytes_write.sum"][2:6]) * unit[rows["dram__bytes_write.sum"][1]]
+    except (KeyError, ValueError):
+        return None, "ncu summary not readable"
+    alg = 66.10e6 + 33.07e6 + 14.18e6 + 9.45e6  # weights + scales + biases of gate+up, down, qkv, o (DESIGN.md section 4)
+    ratio = (rd + wr) / alg
+    return int(alg_bytes_per_launch * ratio), f"ncu --set full capture of 4 launches (traffic / algorithmic = {ratio:.4f})"
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -291,8 +312,10 @@ def run_b200(a):
     if not a.no_kernel_timing:
         qbytes = nums["weight_bytes"] / world  # the qmv launches of a step together read this GPU's weights once
         ach = qbytes / qsec / 1e9
+        traffic, traffic_src = ncu_traffic_per_launch(qbytes / nlaunch, a.bits)
         line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}>", "achieved": round(ach, 1), "peak": peak,
-                            "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None,
+                            "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": traffic,
+                            "traffic_source": traffic_src,
                             "launches_per_step": nlaunch, "avg_launch_us": round(qsec / nlaunch * 1e6, 2),
                             "algorithmic_bytes_per_launch": int(qbytes / nlaunch),
                             "how": "CUDA-event pair around each launch in an eager pass (no graph / PDL)"}
