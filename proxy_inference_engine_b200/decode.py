@@ -240,6 +240,21 @@ class DecodeEngine:
         _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
                                 _p(self.seq), self.seq.shape[1], _stream()), "argmax")
 
+    def enqueue_gemvs(self):
+        """Only the quantized matmuls of one step (4 per layer + head), same descriptors, no collectives: bench.py times
+        a CUDA graph of these to get the dominant kernel's in-graph launch duration (the outputs are scratch)."""
+        a, m = self.args, self.model
+        h, hid, qd = self.h, a.hidden_size, self.Hq * self.D
+        for i, ly in enumerate(m.layers):
+            self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight, EPI_STORE, None)
+            self._qmv(h, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_RESADD, h)
+            self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2, ly.post_attention_layernorm.weight,
+                      EPI_SILUMUL, None)
+            self._qmv(h, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None, EPI_RESADD, h)
+        out = self.logits_local if self.tp_on else self.logits
+        self._qmv(out, out.shape[1], h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+        return 4 * len(m.layers) + 1
+
     def _ensure_graph(self):
         if not self.use_graph or self.graph is not None:
             return
