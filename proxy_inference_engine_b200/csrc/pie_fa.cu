@@ -16,7 +16,7 @@
 
 namespace pie {
 
-constexpr int kFaBQ = 64, kFaBKV = 64, kFaThreads = 128, kFaMaxSplits = 32;
+constexpr int kFaBQ = 64, kFaBKV = 64, kFaThreads = 128, kFaMaxSplits = 32, kFaDecStages = 3;
 
 __device__ __forceinline__ size_t fa_kv_addr(const KvLayout& kv, int b, int h, int t) {
   if (kv.page_table) {
@@ -206,7 +206,7 @@ struct FaDecArgs {
 
 template <int D>
 __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_constant__ FaDecArgs a) {
-  constexpr int KC = D / 16, DT = D / 8, CPR = D / 8, TILE = kFaBKV * D * 2, PW = D + 2;
+  constexpr int KC = D / 16, DT = D / 8, CPR = D / 8, TILE = kFaBKV * D * 2, PW = D + 2, NS = kFaDecStages;
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ int s_last;
   __shared__ float s_m[16][kFaMaxSplits], s_l[16][kFaMaxSplits], s_w[16][kFaMaxSplits];
@@ -218,11 +218,11 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
   const int p = a.pos[b], ctx = p + 1;
   const int tiles = (ctx + kFaBKV - 1) / kFaBKV, per = (tiles + a.nsplit - 1) / a.nsplit;
   const int j0 = split * per, j1 = min(tiles, j0 + per);
-  const uint32_t sK = smem_u32(smem), sV = sK + 2 * TILE;
+  const uint32_t sK = smem_u32(smem), sV = sK + NS * TILE;
 
-  auto issue = [&](int j) {
-    const uint32_t dk = sK + ((j - j0) & 1) * TILE, dv = sV + ((j - j0) & 1) * TILE;
-    for (int i = tid; i < kFaBKV * CPR; i += kFaThreads) {
+  auto issue = [&](int j) {  // always commits one group (empty past the end): the wait below counts groups
+    const uint32_t dk = sK + ((j - j0) % NS) * TILE, dv = sV + ((j - j0) % NS) * TILE;
+    for (int i = tid; j < j1 && i < kFaBKV * CPR; i += kFaThreads) {
       const int r = i / CPR, c = i % CPR;
       const int t = min(j * kFaBKV + r, p);
       const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
     }
     cp_async_commit();
   };
-  if (j0 < j1) issue(j0);
+  for (int s = 0; s < NS - 1; ++s) issue(j0 + s);
 
   // Q fragments: row g = query head qh0 + g (rows >= n_rep are zero)
   uint32_t qf[KC][4];
@@ -253,9 +253,10 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
   for (int j = j0; j < j1; ++j) {
-    if (j + 1 < j1) { issue(j + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    issue(j + NS - 1);
+    cp_async_wait<NS - 1>();
     __syncthreads();
-    const uint32_t tk = sK + ((j - j0) & 1) * TILE, tv = sV + ((j - j0) & 1) * TILE;
+    const uint32_t tk = sK + ((j - j0) % NS) * TILE, tv = sV + ((j - j0) % NS) * TILE;
     float s[2][4];
 #pragma unroll
     for (int n = 0; n < 2; ++n) {
@@ -394,10 +395,12 @@ cudaError_t launch_decode_attn_tc(uint16_t* out, const uint16_t* q, const uint16
   const size_t cnt_bytes = (((size_t)B * Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
   a.ws_cnt = reinterpret_cast<unsigned int*>(ws);
   a.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + cnt_bytes);
-  const size_t smem = (size_t)4 * kFaBKV * D * 2;
+  const size_t smem = (size_t)2 * kFaDecStages * kFaBKV * D * 2;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fa_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kFaBKV * 128 * 2);
+    cudaError_t e = cudaFuncSetAttribute(fa_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kFaDecStages * kFaBKV * 128 * 2);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(fa_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kFaDecStages * kFaBKV * 64 * 2);
     if (e != cudaSuccess) return e;
     configured = true;
   }
