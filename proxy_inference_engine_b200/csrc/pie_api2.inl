@@ -79,9 +79,9 @@ int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context) {
   if (B <= 0 || Hq <= 0 || Hkv <= 0) return 1;
   const int n_rep = Hq / Hkv;
   int ctas, want;
-  if (n_rep <= 16) {  // tensor-core kernel: one CTA per (sequence, kv head, split), 3 resident per SM
+  if (n_rep <= 16) {  // tensor-core kernel: one CTA per (sequence, kv head, split), 2 resident per SM (96 KB of stages)
     ctas = B * Hkv;
-    want = 148 * 3;
+    want = 148 * 2;
   } else {
     const int rg = n_rep % 4 == 0 ? n_rep / 4 : (n_rep % 2 == 0 ? n_rep / 2 : n_rep);
     ctas = B * Hkv * rg;
