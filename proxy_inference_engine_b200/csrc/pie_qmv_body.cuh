@@ -42,7 +42,32 @@ __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* 
   // fused RMSNorm (mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111): inverse rms over the FULL row
   // M <= 2: every thread takes part in each row (one round trip per row).  More rows: a warp per row with 8 loads in
   // flight per lane, all rows concurrently, ONE barrier.  The inverse rms values end up in red[0 .. M).
-  if (a.norm_w) {
+  // Decode fast path (M <= 2, the whole row staged by this CTA, one 16-element block per thread): the block each thread
+  // will stage is loaded ONCE, serves the sum of squares, and stays in registers for the second pass -- one L2 round
+  // trip instead of two in front of every q/k/v and gate/up launch.
+  const int bpr0 = klen / 16;
+  const bool one_pass = a.norm_w && a.M <= 2 && klen == a.K && a.M * bpr0 <= nthr && (bpr0 & 31) == 0;
+  uint4 keep0 = make_uint4(0, 0, 0, 0), keep1 = make_uint4(0, 0, 0, 0);
+  if (one_pass) {
+    float ss = 0.f;
+    if (tid < a.M * bpr0) {
+      const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)(tid / bpr0) * a.x_ld + k0 + (tid % bpr0) * 16);
+      keep0 = ldcg128(src); keep1 = ldcg128(src + 1);
+      const uint32_t u[8] = {keep0.x, keep0.y, keep0.z, keep0.w, keep1.x, keep1.y, keep1.z, keep1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { float lo = bf16lo(u[j]), hi = bf16hi(u[j]); ss += lo * lo + hi * hi; }
+    }
+    ss = warp_sum(ss);
+    if (lane == 0) red[32 + (tid >> 5)] = ss;
+    __syncthreads();
+    if (tid < a.M) {
+      const int wpr = bpr0 >> 5;  // warps per row
+      float tot = 0.f;
+      for (int w = 0; w < wpr; ++w) tot += red[32 + tid * wpr + w];
+      red[tid] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
+    }
+    __syncthreads();
+  } else if (a.norm_w) {
     if (a.M <= 2) {
       float inv2[2] = {0.f, 0.f};
       for (int m = 0; m < a.M; ++m) {
@@ -93,7 +118,9 @@ __device__ void stage_x(const QmvArgs& a, int k0, int klen, uint8_t* xs, float* 
 #pragma unroll
    for (int u = 0; u < 4; ++u) {
      const int idx = (it0 + u) * nthr + tid;
-     if (idx < total) {
+     if (one_pass && it0 + u == 0) {
+       pre[u][0] = keep0; pre[u][1] = keep1;
+     } else if (idx < total) {
        const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)(idx / bpr) * a.x_ld + k0 + (idx % bpr) * 16);
        pre[u][0] = ldcg128(src); pre[u][1] = ldcg128(src + 1);
      }
