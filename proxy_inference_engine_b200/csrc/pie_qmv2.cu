@@ -1,0 +1,784 @@
+// TMA-fed decode GEMV for 4-bit weights, 1 <= M <= 8 activation rows, sm_100a (the decode step's dominant kernel).
+//
+// Replaces mx.quantized_matmul(transpose=True) at decode sizes (QuantizedLinear.__call__,
+// MLX/python/mlx/nn/layers/quantized.py:204-216 -> Metal qmv_fast, MLX/mlx/backend/metal/kernels/quantized.h:623-689):
+//     y[m, n] = bf16( sum_k x[m, k] * (scales[n, k/64] * q[n, k] + biases[n, k/64]) ),  fp32 accumulation.
+//
+// Shape of the kernel (one CTA per SM, 16 warps)
+//   * work unit = 16 weight rows x 512 k: 4 KB of packed weights + 256 B of bf16 scales + 256 B of bf16 biases.  The
+//     CTA owns a contiguous range of whole 16-row tiles; the tiles' units, flattened tile-major, are cut into 16
+//     contiguous runs, one per warp (a tile's K is split over warps whenever the CTA has fewer tiles than warps);
+//   * every warp owns a private two-stage ring fed by TMA: one elected lane issues three cp.async.bulk.tensor copies
+//     per unit (weights as a 3-D box 128 B x 16 rows x 2 chunks in the 32-byte-atom 128-byte swizzle, so that the
+//     fragment loads below are bank-conflict free; scales and biases as 16 B x 16 row boxes) that complete on the
+//     stage's mbarrier (complete_tx).  No cross-warp synchronisation in the main loop, no per-lane address state;
+//   * dequantisation in registers: ((w >> 4i) & 0x000f000f) | 0x43004300 = two bf16 values 128 + q, fed to
+//     mma.sync.m16n8k16 as the A operand (16 weight rows x 16 k); the activations are the B operand (batch rows as
+//     columns), staged once per CTA in fragment order.  The accumulator of a 64-element group starts at
+//     -128 * sum_x(group), so that it ends as sum_k q x exactly as in fp32; y += scale * acc;
+//   * the bias term sum_g biases[n, g] * sum_x(g) is itself a small dense product: one mma.sync.m16n8k8 per unit on
+//     the bf16 biases as they lie in shared memory against sum_x split exactly into three bf16 pieces
+//     (the factoring s * sum(x q) + b * sum(x) of qmv_fast, kernels/quantized.h:225);
+//   * a tile whose K was cut over several warps is summed in warp (= k) order through shared memory at the end of the
+//     kernel: deterministic.  Epilogues from registers: store / residual add / SwiGLU (tiles of 8 gate + 8 up rows);
+//   * programmatic dependent launch: the first two units of every warp are requested before griddepcontrol.wait, x is
+//     read after it; optionally the kernel asks L2 (cp.async.bulk.prefetch.tensor) for the first units of the NEXT
+//     matrix of the step when its own loads have all been issued, so that HBM keeps streaming across the kernel
+//     boundary.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
+#include "pie_internal.h"
+#include "pie_ptx.cuh"
+#include "pie_qmv2.h"
+
+namespace pie {
+
+// ------------------------------------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* map, uint32_t bar, int c0, int c1, int c2,
+                                            uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_b(uint32_t dst, const void* map, uint32_t bar, int c0, int c1, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_3d(const void* map, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(map), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_2d(const void* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_init_s(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_s(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0, ok = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) break;
+    if (++spins > PIE_SPIN_LIMIT) __trap();
+  }
+}
+// D(16x8) += A(16x8, bf16, row) * B(8x8, bf16, col): a0 (g, 2t..2t+1), a1 (g+8, 2t..), b0 (k 2t..2t+1, n g)
+__device__ __forceinline__ void mma_bf16_1688(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(b0));
+}
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t lift4b(uint32_t w, int sh, uint32_t mask, uint32_t magic) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(w >> sh), "r"(mask), "r"(magic));
+  return d;
+}
+
+// ------------------------------------------------------------------------------------------- geometry
+// Dynamic shared memory (base aligned to 1024 B):
+//   [weight stages: warp w, stage s at (2 w + s) * 4096][scale/bias stages: (2 w + s) * 512: 256 B scales, 256 B biases]
+//   [mbarriers 32 x 8 B][edge tile ids 32 x 4 B][reduction scratch 1 KB][-128 * group sums of x][bias-side pieces of the
+//   group sums][x in fragment order]
+constexpr int kQ2SbOff = kQ2Warps * kQ2Stages * kQ2WBytes;               // 131072
+constexpr int kQ2BarOff = kQ2SbOff + kQ2Warps * kQ2Stages * kQ2SbBytes;  // + 16384
+constexpr int kQ2EdgeOff = kQ2BarOff + kQ2Warps * kQ2Stages * 8;
+constexpr int kQ2RedOff = kQ2EdgeOff + kQ2Warps * 2 * 4;
+constexpr int kQ2VarOff = kQ2RedOff + 1024;
+
+__host__ __device__ inline int q2_kpad(int K) { return (K + kQ2UnitK - 1) / kQ2UnitK * kQ2UnitK; }
+__host__ __device__ inline int q2_xrow_bytes(int K) { return q2_kpad(K) * 2 + 16; }
+__host__ __device__ inline int q2_gpitch(int K) { return q2_kpad(K) / kGroup + 8; }  // bf16 elements per pieces row
+
+size_t qmv2_smem_bytes(int M, int K) {
+  const int cols = M == 1 ? 1 : 8;
+  const size_t nsx = (size_t)(q2_kpad(K) / kGroup) * cols * 4;
+  const size_t pieces = ((size_t)3 * cols * q2_gpitch(K) * 2 + 15) & ~(size_t)15;
+  const size_t xs = (size_t)M * q2_xrow_bytes(K);
+  return 1024 /* alignment slack */ + kQ2VarOff + nsx + pieces + xs;
+}
+
+// ------------------------------------------------------------------------------------------- x staging
+// x (optionally RMS-normalised: mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111) -> shared memory in B-fragment order:
+// within every block of 16 k, position 4 m + 2 h + l holds k = m + 8 h + 4 l (what lane t of the MMA needs for step m).
+// Also per 64-element group: the accumulator's start value -OFF * sum(staged x) and sum(x) as three bf16 pieces.
+//
+// F16 = false: x is staged as the bf16 values themselves, weights lift to bf16 128 + q (OFF = 128).
+// F16 = true : x is staged as fp16 after an exact power-of-two scaling of the row (max |x| lands in [2^14, 2^15), so
+//   every element down to 2^-28 of the row maximum converts exactly; smaller ones keep subnormal precision and move the
+//   dot product by less than an fp32 rounding), weights lift to fp16 1024 + q or 1024 + 16 q (two nibble positions
+//   per 16-bit half without a shift; x at odd k is pre-divided by 16), OFF = 1024.  The row scale is undone when a tile
+//   is finished.  Everything the MMA sees is exact in fp32 either way.
+template <bool ONECOL, bool F16>
+__device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, float* red) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NT = kQ2Warps * 32;
+  constexpr int COLS = ONECOL ? 1 : 8;
+  const int kpad = q2_kpad(a.K), G = kpad / kGroup, gp = q2_gpitch(a.K);
+  float* nsx = reinterpret_cast<float*>(var);
+  uint16_t* pieces = reinterpret_cast<uint16_t*>(var + (size_t)G * COLS * 4);
+  uint8_t* xs = var + (size_t)G * COLS * 4 + (((size_t)3 * COLS * gp * 2 + 15) & ~(size_t)15);
+  const int xrow = q2_xrow_bytes(a.K);
+  const int bpr = kpad / 16;           // 16-element blocks per row (multiple of 32)
+  const int total = a.M * bpr;
+  const int nits = (total + NT - 1) / NT;
+  const bool keep = nits <= 4;         // every block of this thread stays in registers between the passes
+  uint4 blk[4][2];
+  auto load_round = [&](int it0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = (it0 + u) * NT + tid;
+      blk[u][0] = blk[u][1] = make_uint4(0, 0, 0, 0);
+      if (idx < total) {
+        const int m = idx / bpr, b = idx - m * bpr;
+        if (b * 16 < a.K) {
+          const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld + b * 16);
+          blk[u][0] = ldcg128(src); blk[u][1] = ldcg128(src + 1);
+        }
+      }
+    }
+  };
+  // per-row reduction of one value per (round, warp): a warp's 32 blocks of a round lie in one row (bpr % 32 == 0)
+  auto row_of_entry = [&](int e) { const int first = (e / kQ2Warps) * NT + (e % kQ2Warps) * 32; return first < total ? first / bpr : -1; };
+  if (a.norm_w) {
+    for (int it0 = 0; it0 < nits; it0 += 4) {
+      load_round(it0);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (it0 + u >= nits) break;
+        const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
+                                blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
+        float ss = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float lo = bf16lo(w8[j]), hi = bf16hi(w8[j]); ss += lo * lo + hi * hi; }
+        ss = warp_sum(ss);
+        if (lane == 0) red[(it0 + u) * kQ2Warps + warp] = ss;
+      }
+    }
+    __syncthreads();
+    if (a.M > 1) {  // one thread per row adds the row's partials in (round, warp) order
+      if (tid < a.M) {
+        float tot = 0.f;
+        for (int e = 0; e < nits * kQ2Warps; ++e)
+          if (row_of_entry(e) == tid) tot += red[e];
+        red[192 + tid] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
+      }
+      __syncthreads();
+    }
+  }
+  float inv1 = 0.f;
+  if (a.norm_w && a.M == 1) {
+    float tot = 0.f;
+    for (int e = 0; e < nits * kQ2Warps; ++e)
+      if (row_of_entry(e) == 0) tot += red[e];
+    inv1 = 1.0f / sqrtf(tot / (float)a.K + a.eps);
+  }
+  // block u of this thread -> its 16 values (normalised when asked), as floats holding bf16 values
+  auto values = [&](int u, int m, int b, bool live, float (&v)[16]) {
+    const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
+                            blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(w8[j]); v[2 * j + 1] = bf16hi(w8[j]); }
+    if (a.norm_w && live) {
+      const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + b * 16);
+      const uint4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
+      const uint32_t wu[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      const float inv = a.M == 1 ? inv1 : red[192 + m];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        v[2 * j] = bfround(bfround(v[2 * j] * inv) * bf16lo(wu[j]));
+        v[2 * j + 1] = bfround(bfround(v[2 * j + 1] * inv) * bf16hi(wu[j]));
+      }
+    }
+  };
+  if (F16) {
+    // (host guarantees nits <= 4: the normalised blocks stay in registers, packed, while the row maxima are reduced)
+    if (!a.norm_w) load_round(0);
+    __syncthreads();  // red[] is reused (the inverse rms values at red[192 ..] stay)
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (u >= nits) break;
+      const int idx = u * NT + tid;
+      const bool ok = idx < total;
+      const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
+      float v[16];
+      values(u, m, b, ok && b * 16 < a.K, v);
+      float amax = 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) amax = fmaxf(amax, fabsf(v[j]));
+      blk[u][0] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+      blk[u][1] = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+      amax = warp_max(amax);
+      if (lane == 0) red[u * kQ2Warps + warp] = amax;
+    }
+    __syncthreads();
+    if (tid < a.M) {
+      float mx = 0.f;
+      for (int e = 0; e < nits * kQ2Warps; ++e)
+        if (row_of_entry(e) == tid) mx = fmaxf(mx, red[e]);
+      // scale = 2^(14 - floor(log2 mx)); 1 for a zero (or denormal / non-finite) row
+      const uint32_t ex = (__float_as_uint(mx) >> 23) & 0xffu;
+      const bool sane = ex >= 16 && ex < 255;
+      red[200 + tid] = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;   // scale
+      red[208 + tid] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;               // 1 / scale
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (u >= nits) break;
+      const int idx = u * NT + tid;
+      const bool ok = idx < total;
+      const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
+      const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
+                              blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(w8[j]); v[2 * j + 1] = bf16hi(w8[j]); }
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) s += v[j];
+      const float sc = red[200 + m], sc16 = sc * 0.0625f;
+      // what the MMA will see: fp16(v * scale), odd k also / 16; its exact sum starts the accumulator
+      uint32_t h[8];  // h[j] = fp16 pair (k = 2j, 2j + 1)
+      float sh = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        __half2 hv = __floats2half2_rn(v[2 * j] * sc, v[2 * j + 1] * sc16);
+        h[j] = *reinterpret_cast<uint32_t*>(&hv);
+        const float2 back = __half22float2(hv);
+        sh += back.x + back.y;
+      }
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      sh += __shfl_xor_sync(0xffffffffu, sh, 1);
+      sh += __shfl_xor_sync(0xffffffffu, sh, 2);
+      if (ok) {
+        // position pair (4 mm + 2 hh, +1) holds k = (mm + 8 hh, mm + 8 hh + 4): halves of h[] regrouped by PRMT
+        uint32_t o[8];
+#pragma unroll
+        for (int mm = 0; mm < 4; ++mm) {
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const int k0 = mm + 8 * hh, k1 = k0 + 4;
+            const uint32_t lo16 = (k0 & 1) ? (h[k0 >> 1] >> 16) : (h[k0 >> 1] & 0xffffu);
+            const uint32_t hi16 = (k1 & 1) ? (h[k1 >> 1] >> 16) : (h[k1 >> 1] & 0xffffu);
+            o[2 * mm + hh] = lo16 | (hi16 << 16);
+          }
+        }
+        uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)m * xrow + b * 32);
+        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        if ((b & 3) == 0) {
+          const int grp = b >> 2;
+          nsx[grp * COLS + m] = -1024.f * sh;
+          const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
+          pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
+          pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
+          pieces[(2 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(lo) >> 16);
+        }
+      }
+    }
+  } else {
+    for (int it0 = 0; it0 < nits; it0 += 4) {
+      if (!(keep && a.norm_w)) load_round(it0);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (it0 + u >= nits) break;
+        const int idx = (it0 + u) * NT + tid;
+        const bool ok = idx < total;
+        const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
+        float v[16];
+        values(u, m, b, ok && b * 16 < a.K, v);
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) s += v[j];
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        if (ok) {
+          uint32_t o[8];
+#pragma unroll
+          for (int mm = 0; mm < 4; ++mm) {
+            o[2 * mm] = pack_bf16(v[mm], v[mm + 4]);
+            o[2 * mm + 1] = pack_bf16(v[mm + 8], v[mm + 12]);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)m * xrow + b * 32);
+          dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+          if ((b & 3) == 0) {
+            const int grp = b >> 2;
+            nsx[grp * COLS + m] = -128.f * s;
+            const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
+            pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
+            pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
+            pieces[(2 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(lo) >> 16);
+          }
+        }
+      }
+    }
+  }
+  if (!ONECOL) {  // columns >= M of the MMA are never stored, but their start values must be finite
+    for (int i = tid; i < G * COLS; i += NT)
+      if ((i & 7) >= a.M) nsx[i] = 0.f;
+    for (int i = tid; i < 3 * COLS * gp; i += NT)
+      if ((i / gp) % COLS >= a.M) pieces[i] = 0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------- the kernel
+template <bool ONECOL, bool F16>
+__global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_constant__ Qmv2Args a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: TMA operands stay in uniform registers
+  const int g = lane >> 2, t = lane & 3;
+  constexpr int COLS = ONECOL ? 1 : 8;
+
+  // ---- this CTA's tiles and this warp's run of units -------------------------------------------------
+  const int G = gridDim.x, c = blockIdx.x;
+  const int tile_lo = (int)((long long)c * a.ntiles / G), tile_hi = (int)((long long)(c + 1) * a.ntiles / G);
+  const int upt = a.upt;
+  const int cu = (tile_hi - tile_lo) * upt;                 // units of this CTA
+  const int ub = tile_lo * upt + (int)((long long)warp * cu / kQ2Warps);
+  const int ue = tile_lo * upt + (int)((long long)(warp + 1) * cu / kQ2Warps);
+
+  const uint32_t smem_s = smem_u32(smem);
+  const uint32_t wst = smem_s + (uint32_t)(warp * kQ2Stages) * kQ2WBytes;
+  const uint32_t sbst = smem_s + kQ2SbOff + (uint32_t)(warp * kQ2Stages) * kQ2SbBytes;
+  const uint32_t bar0 = smem_s + kQ2BarOff + (uint32_t)(warp * kQ2Stages) * 8;
+  int* edge_tile = reinterpret_cast<int*>(smem + kQ2EdgeOff);
+  float* red = reinterpret_cast<float*>(smem + kQ2RedOff);
+  uint8_t* var = smem + kQ2VarOff;
+
+  const uint64_t pol = l2_policy_evict_first();
+  // (tile, k chunk) -> three (dual: six) TMA copies into stage st
+  auto issue = [&](int tile, int kc, int st) {
+    const uint32_t bar = bar0 + st * 8, wd = wst + st * kQ2WBytes, sd = sbst + st * kQ2SbBytes;
+    mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
+    if (a.dual) {
+      const int r0 = tile * 8;
+      tma_load_3d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, pol);
+      tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, pol);
+      tma_load_2d_b(sd, &a.smap[0], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 128, &a.smap[1], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 256, &a.bmap[0], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 384, &a.bmap[1], bar, 8 * kc, r0, pol);
+    } else {
+      int si = 0;
+      if (a.nseg > 1 && tile >= a.tile0[1]) si = 1;
+      if (a.nseg > 2 && tile >= a.tile0[2]) si = 2;
+      const int r0 = (tile - a.tile0[si]) * 16;
+      tma_load_3d(wd, &a.wmap[si], bar, 0, r0, 2 * kc, pol);
+      tma_load_2d_b(sd, &a.smap[si], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 256, &a.bmap[si], bar, 8 * kc, r0, pol);
+    }
+  };
+  // producer cursor (lane 0 only): the next unit to request
+  int p_u = ub, p_tile = ub / upt, p_kc = ub - p_tile * upt;
+  auto issue_next = [&](int st) {
+    issue(p_tile, p_kc, st);
+    ++p_u;
+    if (++p_kc == upt) { p_kc = 0; ++p_tile; }
+  };
+
+  if (lane == 0) {
+    mbar_init_s(bar0, 1);
+    mbar_init_s(bar0 + 8, 1);
+    fence_mbar_init();
+    fence_proxy_async();
+    edge_tile[warp * 2] = -1;
+    edge_tile[warp * 2 + 1] = -1;
+    if (p_u < ue) issue_next(0);
+    if (p_u < ue) issue_next(1);
+  }
+  pdl_launch_dependents();
+  pdl_wait();
+  q2_stage_x<ONECOL, F16>(a, var, red);
+  __syncthreads();
+
+  // ---- per-lane constants -------------------------------------------------------------------------
+  const int kpad = q2_kpad(a.K), Gp = kpad / kGroup, gp = q2_gpitch(a.K);
+  const uint32_t nsx_s = smem_u32(var);
+  const uint32_t pcs_s = nsx_s + (uint32_t)Gp * COLS * 4;
+  const uint32_t xs_s = pcs_s + (uint32_t)((3 * COLS * gp * 2 + 15) & ~15);
+  const int xrow = q2_xrow_bytes(a.K);
+  const int col = ONECOL ? 0 : (g < a.M ? g : 0);
+  const uint32_t x_lane = xs_s + (uint32_t)col * xrow + t * 32;
+  const uint32_t nsx_lane = ONECOL ? nsx_s : nsx_s + 2 * t * 4;
+  const uint32_t pcs_lane = pcs_s + (uint32_t)((ONECOL ? 0 : g) * gp + 2 * t) * 2;
+  const uint32_t hs = a.dual ? 2048u : 1024u, cs = a.dual ? 1024u : 2048u;  // strides: row half, 128-byte chunk
+  uint32_t woff[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) woff[j] = g * 128 + ((j ^ (g & 3)) << 5) + t * 8;
+  const uint32_t lmask = a.lift_mask, lmask2 = a.lift_mask2, lmagic = a.lift_magic;
+
+  float rs[2] = {1.f, 1.f};  // F16: 1 / row scale of activation rows 2t, 2t + 1
+  if (F16) { rs[0] = red[208 + (ONECOL ? 0 : 2 * t)]; rs[1] = red[208 + (ONECOL ? 0 : 2 * t + 1)]; }
+  float ys[4] = {0.f, 0.f, 0.f, 0.f}, yb[4] = {0.f, 0.f, 0.f, 0.f};
+  float e0v[4] = {0.f, 0.f, 0.f, 0.f};
+  int e0_tile = -1;
+  uint32_t res_raw[4] = {0, 0, 0, 0};
+
+  auto seg_of = [&](int tile, int& si, int& nbase) {
+    si = 0;
+    if (a.dual) { nbase = tile * 8; return; }
+    if (a.nseg > 1 && tile >= a.tile0[1]) si = 1;
+    if (a.nseg > 2 && tile >= a.tile0[2]) si = 2;
+    nbase = (tile - a.tile0[si]) * 16;
+  };
+  auto load_residual = [&](int tile) {
+    int si, nbase;
+    seg_of(tile, si, nbase);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int m = 2 * t + (q & 1), n = nbase + g + (q >> 1) * 8;
+      res_raw[q] = 0;
+      if (m < a.M && n < a.N[si] && !(ONECOL && ((q & 1) || t)))
+        res_raw[q] = (uint32_t)a.residual[(size_t)m * a.out_ld + a.out_off[si] + n];
+    }
+  };
+  // epilogue from registers: lane (g, t) holds rows g, g + 8 x activation rows 2t, 2t + 1
+  auto epilogue = [&](int tile, const float (&v)[4]) {
+    int si, nbase;
+    seg_of(tile, si, nbase);
+#pragma unroll
+    for (int cc = 0; cc < (ONECOL ? 1 : 2); ++cc) {
+      const int m = 2 * t + cc;
+      if (m >= a.M) continue;
+      if (a.epi == EPI_SILUMUL) {  // row g = gate, row g + 8 = up of the same output column
+        const int n = nbase + g;
+        if (n < a.N[0]) {
+          const float gt = bfround(v[cc]), up = bfround(v[2 + cc]);
+          const float sg = bfround(1.f / (1.f + expf(-gt)));  // nn.silu = x * sigmoid(x), each op rounded
+          a.out[(size_t)m * a.out_ld + n] = f2bf(bfround(gt * sg) * up);
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int n = nbase + g + 8 * h;
+          if (n < a.N[si]) {
+            float r = bfround(v[2 * h + cc]);
+            if (a.epi == EPI_RESADD) r = bf16lo(res_raw[2 * h + cc]) + r;
+            a.out[(size_t)m * a.out_ld + a.out_off[si] + n] = f2bf(r);
+          }
+        }
+      }
+    }
+  };
+
+  // ---- main loop ---------------------------------------------------------------------------------------
+  int run_start_kc = 0;  // k chunk at which this warp's share of the current tile began
+  bool pf_done = false;
+  int tile = ub / upt, kc = ub - tile * upt;
+  for (int u = ub; u < ue; ++u) {
+    const int i = u - ub, st = i & 1;
+    if (i == 0 || kc == 0) {
+      run_start_kc = kc;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ys[q] = yb[q] = 0.f;
+    }
+    const bool tile_ends = kc == upt - 1 || u == ue - 1;
+    if (a.epi == EPI_RESADD && kc == upt - 1 && run_start_kc == 0) load_residual(tile);
+    mbar_wait_s(bar0 + st * 8, (i >> 1) & 1);
+    const uint32_t wb = wst + st * kQ2WBytes, sb = sbst + st * kQ2SbBytes;
+    const uint4 sA = lds128(sb + g * 16), sB = lds128(sb + 128 + g * 16);
+    const uint32_t sAw[4] = {sA.x, sA.y, sA.z, sA.w}, sBw[4] = {sB.x, sB.y, sB.z, sB.w};
+    const uint32_t xg = x_lane + (uint32_t)kc * (8 * 128);
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) {
+      const int cch = jj >> 2, j = jj & 3;
+      const uint2 w0 = lds64(wb + cch * cs + woff[j]);
+      const uint2 w1 = lds64(wb + cch * cs + woff[j] + hs);
+      const uint4 x0 = lds128(xg + jj * 128), x1 = lds128(xg + jj * 128 + 16);
+      float acc[4];
+      if (ONECOL) {
+        const float n0 = __uint_as_float(lds32(nsx_lane + (uint32_t)(kc * 8 + jj) * 4));
+        acc[0] = acc[1] = acc[2] = acc[3] = n0;
+      } else {
+        const uint2 nn = lds64(nsx_lane + (uint32_t)(kc * 8 + jj) * 32);
+        acc[0] = acc[2] = __uint_as_float(nn.x);
+        acc[1] = acc[3] = __uint_as_float(nn.y);
+      }
+      const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        if (F16) {
+          const int sh = (m >> 1) * 8;
+          const uint32_t mk = (m & 1) ? lmask2 : lmask;
+          const uint32_t a0 = lift4b(w0.x, sh, mk, lmagic), a1 = lift4b(w1.x, sh, mk, lmagic),
+                         a2 = lift4b(w0.y, sh, mk, lmagic), a3 = lift4b(w1.y, sh, mk, lmagic);
+          mma_f16_16816(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1]);
+        } else {
+          const uint32_t a0 = lift4b(w0.x, 4 * m, lmask, lmagic), a1 = lift4b(w1.x, 4 * m, lmask, lmagic),
+                         a2 = lift4b(w0.y, 4 * m, lmask, lmagic), a3 = lift4b(w1.y, 4 * m, lmask, lmagic);
+          mma_bf16_16816(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1]);
+        }
+      }
+      const float s0 = jj & 1 ? bf16hi(sAw[jj >> 1]) : bf16lo(sAw[jj >> 1]);
+      const float s1 = jj & 1 ? bf16hi(sBw[jj >> 1]) : bf16lo(sBw[jj >> 1]);
+      ys[0] = fmaf(s0, acc[0], ys[0]);
+      ys[2] = fmaf(s1, acc[2], ys[2]);
+      if (!ONECOL) {
+        ys[1] = fmaf(s0, acc[1], ys[1]);
+        ys[3] = fmaf(s1, acc[3], ys[3]);
+      }
+    }
+    {  // bias term: biases (16 rows x 8 groups, as they lie in the stage) x the three pieces of sum_x
+      const uint32_t ba0 = lds32(sb + 256 + g * 16 + t * 4), ba1 = lds32(sb + 384 + g * 16 + t * 4);
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        const uint32_t b0 = lds32(pcs_lane + (uint32_t)(p * COLS * gp + kc * 8) * 2);
+        mma_bf16_1688(yb, ba0, ba1, b0);
+      }
+    }
+    __syncwarp();
+    if (lane == 0 && p_u < ue) issue_next(st);
+    if (a.pf_on && !pf_done && u + 2 >= ue) {  // all own loads are out: ask L2 for this warp's first units of the next matrix
+      pf_done = true;
+      if (lane == 0) {
+        const int pG = gridDim.x;
+        const int ptl = (int)((long long)c * a.pf_ntiles / pG), pth = (int)((long long)(c + 1) * a.pf_ntiles / pG);
+        const int pcu = (pth - ptl) * a.pf_upt;
+        const int pb = ptl * a.pf_upt + (int)((long long)warp * pcu / kQ2Warps);
+        const int pe = ptl * a.pf_upt + (int)((long long)(warp + 1) * pcu / kQ2Warps);
+        int p0 = pb + a.pf_first, p1 = p0 + a.pf_count;
+        if (p1 > pe) p1 = pe;
+        for (int pu = p0; pu < p1; ++pu) {
+          const int ptile = pu / a.pf_upt, pkc = pu - ptile * a.pf_upt;
+          if (a.pf_dual) {
+            tma_prefetch_3d(&a.pf_wmap[0], 0, ptile * 8, 2 * pkc);
+            tma_prefetch_3d(&a.pf_wmap[1], 0, ptile * 8, 2 * pkc);
+            tma_prefetch_2d(&a.pf_smap[0], 8 * pkc, ptile * 8);
+            tma_prefetch_2d(&a.pf_smap[1], 8 * pkc, ptile * 8);
+            tma_prefetch_2d(&a.pf_bmap[0], 8 * pkc, ptile * 8);
+            tma_prefetch_2d(&a.pf_bmap[1], 8 * pkc, ptile * 8);
+          } else {
+            int si = 0;
+            if (a.pf_nseg > 1 && ptile >= a.pf_tile0[1]) si = 1;
+            if (a.pf_nseg > 2 && ptile >= a.pf_tile0[2]) si = 2;
+            const int r0 = (ptile - a.pf_tile0[si]) * 16;
+            tma_prefetch_3d(&a.pf_wmap[si], 0, r0, 2 * pkc);
+            tma_prefetch_2d(&a.pf_smap[si], 8 * pkc, r0);
+            tma_prefetch_2d(&a.pf_bmap[si], 8 * pkc, r0);
+          }
+        }
+      }
+    }
+    const int kc_done = kc, tile_done = tile;
+    if (++kc == upt) { kc = 0; ++tile; }
+    if (!tile_ends) continue;
+    // ---- this warp's share of the tile is complete ---------------------------------------------------
+    float v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) v[q] = F16 ? fmaf(ys[q], rs[q & 1], yb[q]) : ys[q] + yb[q];
+    if (run_start_kc == 0 && kc_done == upt - 1) {
+      epilogue(tile_done, v);
+    } else if (e0_tile < 0) {
+      // first partial share of this warp: parked in registers until the ring is idle
+      e0_tile = tile_done;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) e0v[q] = v[q];
+    } else {
+      // second partial share (the run's last tile): straight to this warp's stage 1 (its loads have all landed)
+      __syncwarp();
+      asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(wst + kQ2WBytes + lane * 16), "f"(v[0]), "f"(v[1]),
+                   "f"(v[2]), "f"(v[3]) : "memory");
+      if (lane == 0) edge_tile[warp * 2 + 1] = tile_done;
+    }
+  }
+  // park the first edge in this warp's stage 0 (every stage of this warp has been consumed by now)
+  if (e0_tile >= 0) {
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(wst + lane * 16), "f"(e0v[0]), "f"(e0v[1]), "f"(e0v[2]),
+                 "f"(e0v[3]) : "memory");
+    if (lane == 0) edge_tile[warp * 2] = e0_tile;
+  }
+  // the warp whose run holds a cut tile's LAST unit adds the tile's shares in warp (= k) order and finishes it
+  int fin_tile = -1;
+  if (e0_tile >= 0 && (e0_tile + 1) * upt <= ue) fin_tile = e0_tile;   // edge 0 ends inside this run
+  if (fin_tile >= 0 && a.epi == EPI_RESADD) load_residual(fin_tile);
+  __syncthreads();
+  if (fin_tile >= 0) {
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int w2 = 0; w2 <= warp; ++w2) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        if (edge_tile[w2 * 2 + e] != fin_tile) continue;
+        const uint4 p = lds128(smem_s + (uint32_t)(w2 * kQ2Stages + e) * kQ2WBytes + lane * 16);
+        v[0] += __uint_as_float(p.x); v[1] += __uint_as_float(p.y);
+        v[2] += __uint_as_float(p.z); v[3] += __uint_as_float(p.w);
+      }
+    }
+    epilogue(fin_tile, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr; int N, K, rows, kind;
+  bool operator==(const MapKey& o) const { return ptr == o.ptr && N == o.N && K == o.K && rows == o.rows && kind == o.kind; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    h ^= (size_t)k.N * 0x9E3779B97F4A7C15ull + (size_t)k.K * 0xC2B2AE3D27D4EB4Full + (size_t)k.rows * 131 + k.kind;
+    return h;
+  }
+};
+// kind 0: packed 4-bit weights [N, K/2 bytes] as (128 B, rows, K/256 chunks); kind 1: bf16 scales / biases [N, K/64]
+static bool get_map(CUtensorMap* out, const void* ptr, int N, int K, int rows, int kind) {
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  static std::mutex mu;
+  const MapKey key{ptr, N, K, rows, kind};
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return true; }
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  CUtensorMap m;
+  CUresult r;
+  if (kind == 0) {
+    const cuuint64_t dims[3] = {128, (cuuint64_t)N, (cuuint64_t)(K / 256)};
+    const cuuint64_t strides[2] = {(cuuint64_t)(K / 2), 128};
+    const cuuint32_t box[3] = {128, (cuuint32_t)rows, 2};
+    const cuuint32_t es[3] = {1, 1, 1};
+    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(ptr), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    const cuuint64_t dims[2] = {(cuuint64_t)(K / 64), (cuuint64_t)N};
+    const cuuint64_t strides[1] = {(cuuint64_t)(K / 64) * 2};
+    const cuuint32_t box[2] = {8, (cuuint32_t)rows};
+    const cuuint32_t es[2] = {1, 1};
+    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (r != CUDA_SUCCESS) return false;
+  if (cache.size() > 65536) cache.clear();
+  cache.emplace(key, m);
+  *out = m;
+  return true;
+}
+
+bool qmv2_supported(int M, int K, int bits, int group_size, const pie_qmv_seg* segs, int nseg, int dual) {
+  if (bits != 4 || group_size != 64 || M < 1 || M > 8 || K % kQ2UnitK != 0) return false;
+  if (qmv2_smem_bytes(M, K) > (size_t)kQmvMaxSmem) return false;
+  for (int i = 0; i < nseg; ++i) {
+    if ((reinterpret_cast<uintptr_t>(segs[i].wq) & 15) || (reinterpret_cast<uintptr_t>(segs[i].scales) & 15) ||
+        (reinterpret_cast<uintptr_t>(segs[i].biases) & 15))
+      return false;
+  }
+  (void)dual;
+  return encode_fn() != nullptr;
+}
+
+// Fill the matrix part of a descriptor (maps, tiling).  Returns false when a tensor map cannot be encoded.
+static bool fill_matrix(CUtensorMap* wmap, CUtensorMap* smap, CUtensorMap* bmap, int* N, int* tile0, int* out_off,
+                        int& ntiles, const pie_qmv_seg* segs, int nseg, int K, int dual) {
+  int tile = 0, off = 0;
+  for (int i = 0; i < nseg; ++i) {
+    const int rows = dual ? 8 : 16;
+    if (!get_map(&wmap[i], segs[i].wq, segs[i].N, K, rows, 0)) return false;
+    if (!get_map(&smap[i], segs[i].scales, segs[i].N, K, rows, 1)) return false;
+    if (!get_map(&bmap[i], segs[i].biases, segs[i].N, K, rows, 1)) return false;
+    N[i] = segs[i].N; tile0[i] = tile; out_off[i] = off;
+    tile += (segs[i].N + 15) / 16;
+    off += segs[i].N;
+  }
+  ntiles = dual ? (segs[0].N + 7) / 8 : tile;
+  return true;
+}
+
+int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs,
+                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual,
+                    const pie_qmv_next* next) {
+  memset(&a, 0, sizeof(a));
+  const int dual = epilogue == EPI_SILUMUL;
+  if (!fill_matrix(a.wmap, a.smap, a.bmap, a.N, a.tile0, a.out_off, a.ntiles, segs, nseg, K, dual)) return PIE_EUNSUPPORTED;
+  a.nseg = nseg; a.dual = dual; a.M = M; a.K = K; a.upt = q2_kpad(K) / kQ2UnitK;
+  a.x = (const uint16_t*)x; a.x_ld = x_ld;
+  a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
+  a.out = (uint16_t*)out; a.out_ld = out_ld; a.residual = (const uint16_t*)residual; a.epi = epilogue;
+  // fp16 staging of x (see q2_stage_x) needs every block of a thread in registers: M * kpad / 16 <= 4 * 512 blocks
+  static const int f16_env = getenv("PIE_QMV2_F16") ? atoi(getenv("PIE_QMV2_F16")) : 1;
+  a.f16 = f16_env && (long long)M * q2_kpad(K) / 16 <= 4 * kQ2Warps * 32;
+  a.lift_mask = 0x000f000fu; a.lift_mask2 = 0x00f000f0u; a.lift_magic = a.f16 ? 0x64006400u : 0x43004300u;
+  if (next && next->nseg > 0 && next->count > 0) {
+    const int ndual = next->dual;
+    int n_[kMaxSeg], off_[kMaxSeg];
+    if (next->K % kQ2UnitK == 0 &&
+        fill_matrix(a.pf_wmap, a.pf_smap, a.pf_bmap, n_, a.pf_tile0, off_, a.pf_ntiles, next->segs, next->nseg, next->K, ndual)) {
+      a.pf_on = 1; a.pf_nseg = next->nseg; a.pf_dual = ndual; a.pf_upt = q2_kpad(next->K) / kQ2UnitK;
+      a.pf_first = next->first; a.pf_count = next->count;
+    }
+  }
+  return PIE_OK;
+}
+
+template <bool ONECOL, bool F16>
+static cudaError_t launch_qmv2_t(const Qmv2Args& a, bool pdl, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(qmv2_kernel<ONECOL, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQmvMaxSmem);
+  if (e != cudaSuccess) return e;
+  int grid = num_sms();
+  if (grid > a.ntiles) grid = a.ntiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3(kQ2Warps * 32, 1, 1);
+  cfg.dynamicSmemBytes = qmv2_smem_bytes(a.M, a.K);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, qmv2_kernel<ONECOL, F16>, a);
+}
+
+cudaError_t launch_qmv2(const Qmv2Args& a, bool pdl, cudaStream_t st) {
+  if (a.f16) return a.M == 1 ? launch_qmv2_t<true, true>(a, pdl, st) : launch_qmv2_t<false, true>(a, pdl, st);
+  return a.M == 1 ? launch_qmv2_t<true, false>(a, pdl, st) : launch_qmv2_t<false, false>(a, pdl, st);
+}
+
+}  // namespace pie
