@@ -93,20 +93,6 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
                   const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl,
                   void* stream);
 
-/* pie_qmv_fused plus a description of the NEXT quantized matrix the stream will run (the decode step knows its own
- * order): once a CTA has issued its last own load it asks L2 for the units [first_unit, first_unit + unit_count) that
- * each of its warps will read first in that next launch (a unit = 16 rows x 512 k), so that HBM keeps streaming
- * across the kernel boundary.  Only a hint: next_host == NULL, or a shape the TMA path does not serve, is the plain call. */
-typedef struct pie_qmv_next {
-  const pie_qmv_seg* segs;  /* host array, as for pie_qmv_fused */
-  int nseg, K, dual;        /* dual = 1: the next launch is the SwiGLU form (gate, up) */
-  int first, count;         /* units per warp to request, in that launch's own order */
-} pie_qmv_next;
-int pie_qmv_fused_pf(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs_host,
-                     int nseg, int group_size, int bits, const void* norm_weight, float eps, int epilogue,
-                     const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl,
-                     const pie_qmv_next* next_host, void* stream);
-
 /* ---- a3  mx.quantized_matmul for prefill-sized M (replaces Metal qmm_t, kernels/quantized.h:954-1078) -
  * Same contraction and workspace contract as pie_qmv.  x bf16 [M, K] row-major, y bf16 [M, N].           */
 int pie_qmm(void* y, const void* x, const uint32_t* wq, const void* scales, const void* biases, int M, int N,

@@ -10,7 +10,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpie_b200.so")
+LIB_PATH = os.environ.get("PIE_LIB") or os.path.join(_HERE, "libpie_b200.so")  # PIE_LIB: experiment builds
 CSRC = os.path.join(_HERE, "csrc")
 
 PIE_OK = 0
@@ -22,12 +22,6 @@ DTYPE_BF16, DTYPE_F32 = 0, 1
 
 class QmvSeg(C.Structure):
     _fields_ = [("wq", C.c_void_p), ("scales", C.c_void_p), ("biases", C.c_void_p), ("N", C.c_int)]
-
-
-class QmvNext(C.Structure):
-    """pie_qmv_next"""
-    _fields_ = [("segs", C.POINTER(QmvSeg)), ("nseg", C.c_int), ("K", C.c_int), ("dual", C.c_int),
-                ("first", C.c_int), ("count", C.c_int)]
 
 
 class KvLayout(C.Structure):
@@ -72,8 +66,6 @@ SIGNATURES = {
     "pie_qmv": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "pie_qmv_fused": (_i, [_vp, _i, _vp, _i, _i, _i, C.POINTER(QmvSeg), _i, _i, _i, _vp, _f, _i, _vp, _i, _vp,
                            _sz, _i, _vp]),
-    "pie_qmv_fused_pf": (_i, [_vp, _i, _vp, _i, _i, _i, C.POINTER(QmvSeg), _i, _i, _i, _vp, _f, _i, _vp, _i, _vp,
-                              _sz, _i, C.POINTER(QmvNext), _vp]),
     "pie_qmm": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "pie_rms_norm": (_i, [_vp, _vp, _vp, _ll, _i, _f, _vp]),
     "pie_rope": (_i, [_vp, _vp, _ll, _i, _i, _i, _i, _f, _f, _i, _vp, _vp]),

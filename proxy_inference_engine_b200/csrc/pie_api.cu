@@ -200,14 +200,6 @@ size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int du
 int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
                   int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
                   int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
-  return pie_qmv_fused_pf(out, out_ld, x, x_ld, M, K, segs, nseg, group_size, bits, norm_weight, eps, epilogue, residual,
-                          ksplit_hint, workspace, workspace_bytes, pdl, nullptr, stream);
-}
-
-int pie_qmv_fused_pf(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
-                     int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
-                     int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, const pie_qmv_next* next,
-                     void* stream) {
   if (M == 0) return PIE_OK;
   for (int m0 = 0; m0 < M; m0 += kMaxBatch) {
     const int mb = M - m0 < kMaxBatch ? M - m0 : kMaxBatch;
@@ -216,12 +208,17 @@ int pie_qmv_fused_pf(void* out, int out_ld, const void* x, int x_ld, int M, int 
     const int st0 = build_qmv_args(a, p, out, out_ld, x, x_ld, m0, mb, K, segs, nseg, group_size, bits, norm_weight, eps,
                                    epilogue, residual, ksplit_hint, workspace, workspace_bytes, 0);
     if (st0 != PIE_OK) return st0;
-    // TMA-fed GEMV (pie_qmv2.cu): 4-bit weights, up to 8 rows, K a multiple of 512.  PIE_QMV2=0 keeps the cp.async kernel.
-    if (M <= 8 && env_int("PIE_QMV2", 1) && qmv2_supported(mb, K, bits, group_size, segs, nseg, a.dual) &&
-        x_ld % 8 == 0) {
+    // TMA-fed GEMV (pie_qmv2.cu): 4-bit weights, up to 8 rows, K a multiple of 512.  PIE_QMV2: 0 = never (the cp.async
+    // kernel below), 1 = where it measured faster on B200 at one row (us, cp.async / TMA: gate+up 18.9 / 18.1, down 13.1 /
+    // 12.0, head 64.2 / 51.3; the small q/k/v and o matrices are launch-latency bound and 0.1 - 1 us faster on the
+    // cp.async kernel, whose launch descriptor is a tenth of the size), 2 = wherever it is supported.
+    const int q2_mode = env_int("PIE_QMV2", 1);
+    long long q2_elems = 0;
+    for (int i = 0; i < nseg; ++i) q2_elems += (long long)segs[i].N * K;
+    if (M <= 8 && x_ld % 8 == 0 && q2_mode && (q2_mode == 2 || q2_elems >= (32LL << 20)) &&
+        qmv2_supported(mb, K, bits, group_size, segs, nseg, a.dual)) {
       Qmv2Args a2;
-      const int st1 = build_qmv2_args(a2, out, out_ld, x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue, residual,
-                                      env_int("PIE_QMV2_PF", 1) ? next : nullptr);
+      const int st1 = build_qmv2_args(a2, out, out_ld, x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue, residual);
       if (st1 == PIE_OK) {
         const int st2 = cuda_status(launch_qmv2(a2, pdl != 0, (cudaStream_t)stream));
         if (st2 != PIE_OK) return st2;

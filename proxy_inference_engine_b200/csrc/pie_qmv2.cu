@@ -22,9 +22,8 @@
 //   * a tile whose K was cut over several warps is summed in warp (= k) order through shared memory at the end of the
 //     kernel: deterministic.  Epilogues from registers: store / residual add / SwiGLU (tiles of 8 gate + 8 up rows);
 //   * programmatic dependent launch: the first two units of every warp are requested before griddepcontrol.wait, x is
-//     read after it; optionally the kernel asks L2 (cp.async.bulk.prefetch.tensor) for the first units of the NEXT
-//     matrix of the step when its own loads have all been issued, so that HBM keeps streaming across the kernel
-//     boundary.
+//     read after it.  (Asking L2 for the first units of the NEXT matrix of the step with cp.async.bulk.prefetch.tensor
+//     once a warp's own loads were out was tried and measured slower by 0.5 - 1.8 us per launch: removed.)
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -53,20 +52,14 @@ __device__ __forceinline__ void tma_load_2d_b(uint32_t dst, const void* map, uin
       " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(pol)
       : "memory");
 }
-__device__ __forceinline__ void tma_prefetch_3d(const void* map, int c0, int c1, int c2) {
-  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(map), "r"(c0), "r"(c1), "r"(c2)
-               : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_2d(const void* map, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
-}
 __device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_init_s(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
-__device__ __forceinline__ void mbar_wait_s(uint32_t bar, uint32_t parity) {
+// returns 0 through a value the compiler cannot see through (the loads of the stage are made to depend on it)
+__device__ __forceinline__ uint32_t mbar_wait_s(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0, ok = 0;
   while (true) {
     asm volatile(
@@ -79,20 +72,48 @@ __device__ __forceinline__ void mbar_wait_s(uint32_t bar, uint32_t parity) {
     if (ok) break;
     if (++spins > PIE_SPIN_LIMIT) __trap();
   }
+  return ok - 1;
 }
-// D(16x8) += A(16x8, bf16, row) * B(8x8, bf16, col): a0 (g, 2t..2t+1), a1 (g+8, 2t..), b0 (k 2t..2t+1, n g)
-__device__ __forceinline__ void mma_bf16_1688(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a0), "r"(a1), "r"(b0));
+// D(16x8) = A(16x8, bf16, row) * B(8x8, bf16, col) + C: a0 (g, 2t..2t+1), a1 (g+8, 2t..), b0 (k 2t..2t+1, n g).
+// Not volatile, C separate from D: the compiler interleaves the independent accumulator chains of a unit.
+__device__ __forceinline__ void mma_bf16_1688(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0, const float (&c)[4]) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%8,%9,%10};"
+      : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+      : "r"(a0), "r"(a1), "r"(b0), "f"(c[0]), "f"(c[1]), "f"(c[2]), "f"(c[3]));
 }
-__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
-                                              uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+template <bool F16>
+__device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                          uint32_t b1, float c0, float c1, float c2, float c3) {
+  if (F16)
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c0), "f"(c1), "f"(c2), "f"(c3));
+  else
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c0), "f"(c1), "f"(c2), "f"(c3));
+}
+// Shared-memory loads that the compiler may schedule freely AFTER the value `tok` exists (tok = 0, produced by the
+// mbarrier wait: nothing is hoisted above the wait; a later TMA issue is an asm volatile with a memory clobber).
+__device__ __forceinline__ uint2 lds64_t(uint32_t addr, uint32_t tok) {
+  uint2 v;
+  asm("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr + tok));
+  return v;
+}
+__device__ __forceinline__ uint4 lds128_t(uint32_t addr, uint32_t tok) {
+  uint4 v;
+  asm("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr + tok));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32_t(uint32_t addr, uint32_t tok) {
+  uint32_t v;
+  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr + tok));
+  return v;
+}
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred;
 }
 __device__ __forceinline__ uint32_t lift4b(uint32_t w, int sh, uint32_t mask, uint32_t magic) {
   uint32_t d;
@@ -117,7 +138,7 @@ __host__ __device__ inline int q2_gpitch(int K) { return q2_kpad(K) / kGroup + 8
 
 size_t qmv2_smem_bytes(int M, int K) {
   const int cols = M == 1 ? 1 : 8;
-  const size_t nsx = (size_t)(q2_kpad(K) / kGroup) * cols * 4;
+  const size_t nsx = (size_t)(q2_kpad(K) / kGroup) * (cols == 1 ? 16 : 64);  // start values as register quads
   const size_t pieces = ((size_t)3 * cols * q2_gpitch(K) * 2 + 15) & ~(size_t)15;
   const size_t xs = (size_t)M * q2_xrow_bytes(K);
   return 1024 /* alignment slack */ + kQ2VarOff + nsx + pieces + xs;
@@ -140,9 +161,18 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
   constexpr int NT = kQ2Warps * 32;
   constexpr int COLS = ONECOL ? 1 : 8;
   const int kpad = q2_kpad(a.K), G = kpad / kGroup, gp = q2_gpitch(a.K);
+  constexpr int NSXB = ONECOL ? 16 : 64;  // bytes of start values per group: quads {n[2t], n[2t+1], n[2t], n[2t+1]}, t = 0..3
   float* nsx = reinterpret_cast<float*>(var);
-  uint16_t* pieces = reinterpret_cast<uint16_t*>(var + (size_t)G * COLS * 4);
-  uint8_t* xs = var + (size_t)G * COLS * 4 + (((size_t)3 * COLS * gp * 2 + 15) & ~(size_t)15);
+  uint16_t* pieces = reinterpret_cast<uint16_t*>(var + (size_t)G * NSXB);
+  uint8_t* xs = var + (size_t)G * NSXB + (((size_t)3 * COLS * gp * 2 + 15) & ~(size_t)15);
+  auto put_nsx = [&](int grp, int m, float v) {
+    if (ONECOL) {
+      *reinterpret_cast<float4*>(nsx + grp * 4) = make_float4(v, v, v, v);
+    } else {
+      float* q = nsx + grp * 16 + (m >> 1) * 4 + (m & 1);
+      q[0] = v; q[2] = v;
+    }
+  };
   const int xrow = q2_xrow_bytes(a.K);
   const int bpr = kpad / 16;           // 16-element blocks per row (multiple of 32)
   const int total = a.M * bpr;
@@ -163,8 +193,9 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
       }
     }
   };
-  // per-row reduction of one value per (round, warp): a warp's 32 blocks of a round lie in one row (bpr % 32 == 0)
-  auto row_of_entry = [&](int e) { const int first = (e / kQ2Warps) * NT + (e % kQ2Warps) * 32; return first < total ? first / bpr : -1; };
+  // Per-row reductions: entry e = (round, warp) holds the value of blocks [32 e, 32 e + 32), which lie in one row
+  // (bpr % 32 == 0), so row m owns the entries [m * epr, (m + 1) * epr).  Warp m reduces row m: fixed order.
+  const int epr = bpr / 32;
   if (a.norm_w) {
     for (int it0 = 0; it0 < nits; it0 += 4) {
       load_round(it0);
@@ -181,22 +212,13 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
       }
     }
     __syncthreads();
-    if (a.M > 1) {  // one thread per row adds the row's partials in (round, warp) order
-      if (tid < a.M) {
-        float tot = 0.f;
-        for (int e = 0; e < nits * kQ2Warps; ++e)
-          if (row_of_entry(e) == tid) tot += red[e];
-        red[192 + tid] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
-      }
-      __syncthreads();
+    if (warp < a.M) {
+      float tot = 0.f;
+      for (int e = warp * epr + lane; e < (warp + 1) * epr; e += 32) tot += red[e];
+      tot = warp_sum(tot);
+      if (lane == 0) red[192 + warp] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
     }
-  }
-  float inv1 = 0.f;
-  if (a.norm_w && a.M == 1) {
-    float tot = 0.f;
-    for (int e = 0; e < nits * kQ2Warps; ++e)
-      if (row_of_entry(e) == 0) tot += red[e];
-    inv1 = 1.0f / sqrtf(tot / (float)a.K + a.eps);
+    __syncthreads();
   }
   // block u of this thread -> its 16 values (normalised when asked), as floats holding bf16 values
   auto values = [&](int u, int m, int b, bool live, float (&v)[16]) {
@@ -208,7 +230,7 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
       const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + b * 16);
       const uint4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
       const uint32_t wu[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-      const float inv = a.M == 1 ? inv1 : red[192 + m];
+      const float inv = red[192 + m];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         v[2 * j] = bfround(bfround(v[2 * j] * inv) * bf16lo(wu[j]));
@@ -219,7 +241,6 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
   if (F16) {
     // (host guarantees nits <= 4: the normalised blocks stay in registers, packed, while the row maxima are reduced)
     if (!a.norm_w) load_round(0);
-    __syncthreads();  // red[] is reused (the inverse rms values at red[192 ..] stay)
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (u >= nits) break;
@@ -237,15 +258,17 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
       if (lane == 0) red[u * kQ2Warps + warp] = amax;
     }
     __syncthreads();
-    if (tid < a.M) {
+    if (warp < a.M) {
       float mx = 0.f;
-      for (int e = 0; e < nits * kQ2Warps; ++e)
-        if (row_of_entry(e) == tid) mx = fmaxf(mx, red[e]);
+      for (int e = warp * epr + lane; e < (warp + 1) * epr; e += 32) mx = fmaxf(mx, red[e]);
+      mx = warp_max(mx);
       // scale = 2^(14 - floor(log2 mx)); 1 for a zero (or denormal / non-finite) row
       const uint32_t ex = (__float_as_uint(mx) >> 23) & 0xffu;
       const bool sane = ex >= 16 && ex < 255;
-      red[200 + tid] = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;   // scale
-      red[208 + tid] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;               // 1 / scale
+      if (lane == 0) {
+        red[200 + warp] = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;   // scale
+        red[208 + warp] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;               // 1 / scale
+      }
     }
     __syncthreads();
 #pragma unroll
@@ -295,7 +318,7 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
         dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
         if ((b & 3) == 0) {
           const int grp = b >> 2;
-          nsx[grp * COLS + m] = -1024.f * sh;
+          put_nsx(grp, m, -1024.f * sh);
           const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
           pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
           pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
@@ -331,7 +354,7 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
           dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
           if ((b & 3) == 0) {
             const int grp = b >> 2;
-            nsx[grp * COLS + m] = -128.f * s;
+            put_nsx(grp, m, -128.f * s);
             const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
             pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
             pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
@@ -342,15 +365,15 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
     }
   }
   if (!ONECOL) {  // columns >= M of the MMA are never stored, but their start values must be finite
-    for (int i = tid; i < G * COLS; i += NT)
-      if ((i & 7) >= a.M) nsx[i] = 0.f;
+    for (int i = tid; i < G * 8; i += NT)
+      if ((i & 7) >= a.M) put_nsx(i >> 3, i & 7, 0.f);
     for (int i = tid; i < 3 * COLS * gp; i += NT)
       if ((i / gp) % COLS >= a.M) pieces[i] = 0;
   }
 }
 
 // ------------------------------------------------------------------------------------------- the kernel
-template <bool ONECOL, bool F16>
+template <bool ONECOL, bool F16, bool DUAL>
 __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_constant__ Qmv2Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -379,8 +402,18 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   // (tile, k chunk) -> three (dual: six) TMA copies into stage st
   auto issue = [&](int tile, int kc, int st) {
     const uint32_t bar = bar0 + st * 8, wd = wst + st * kQ2WBytes, sd = sbst + st * kQ2SbBytes;
+    if (a.dbg & 2) {  // experiment: weights only
+      mbar_expect_tx_s(bar, kQ2WBytes);
+      if (DUAL) {
+        tma_load_3d(wd, &a.wmap[0], bar, 0, tile * 8, 2 * kc, pol);
+        tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, tile * 8, 2 * kc, pol);
+      } else {
+        tma_load_3d(wd, &a.wmap[0], bar, 0, (tile - a.tile0[0]) * 16, 2 * kc, pol);
+      }
+      return;
+    }
     mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
-    if (a.dual) {
+    if (DUAL) {
       const int r0 = tile * 8;
       tma_load_3d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, pol);
       tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, pol);
@@ -400,8 +433,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   };
   // producer cursor (lane 0 only): the next unit to request
   int p_u = ub, p_tile = ub / upt, p_kc = ub - p_tile * upt;
-  auto issue_next = [&](int st) {
-    issue(p_tile, p_kc, st);
+  auto advance = [&]() {
     ++p_u;
     if (++p_kc == upt) { p_kc = 0; ++p_tile; }
   };
@@ -413,9 +445,9 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     fence_proxy_async();
     edge_tile[warp * 2] = -1;
     edge_tile[warp * 2 + 1] = -1;
-    if (p_u < ue) issue_next(0);
-    if (p_u < ue) issue_next(1);
   }
+  if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
+  if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
   pdl_launch_dependents();
   pdl_wait();
   q2_stage_x<ONECOL, F16>(a, var, red);
@@ -424,14 +456,14 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   // ---- per-lane constants -------------------------------------------------------------------------
   const int kpad = q2_kpad(a.K), Gp = kpad / kGroup, gp = q2_gpitch(a.K);
   const uint32_t nsx_s = smem_u32(var);
-  const uint32_t pcs_s = nsx_s + (uint32_t)Gp * COLS * 4;
+  const uint32_t pcs_s = nsx_s + (uint32_t)Gp * (ONECOL ? 16 : 64);
   const uint32_t xs_s = pcs_s + (uint32_t)((3 * COLS * gp * 2 + 15) & ~15);
   const int xrow = q2_xrow_bytes(a.K);
   const int col = ONECOL ? 0 : (g < a.M ? g : 0);
   const uint32_t x_lane = xs_s + (uint32_t)col * xrow + t * 32;
-  const uint32_t nsx_lane = ONECOL ? nsx_s : nsx_s + 2 * t * 4;
+  const uint32_t nsx_lane = ONECOL ? nsx_s : nsx_s + t * 16;
   const uint32_t pcs_lane = pcs_s + (uint32_t)((ONECOL ? 0 : g) * gp + 2 * t) * 2;
-  const uint32_t hs = a.dual ? 2048u : 1024u, cs = a.dual ? 1024u : 2048u;  // strides: row half, 128-byte chunk
+  constexpr uint32_t hs = DUAL ? 2048u : 1024u, cs = DUAL ? 1024u : 2048u;  // strides: row half, 128-byte chunk
   uint32_t woff[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) woff[j] = g * 128 + ((j ^ (g & 3)) << 5) + t * 8;
@@ -446,7 +478,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
 
   auto seg_of = [&](int tile, int& si, int& nbase) {
     si = 0;
-    if (a.dual) { nbase = tile * 8; return; }
+    if (DUAL) { nbase = tile * 8; return; }
     if (a.nseg > 1 && tile >= a.tile0[1]) si = 1;
     if (a.nseg > 2 && tile >= a.tile0[2]) si = 2;
     nbase = (tile - a.tile0[si]) * 16;
@@ -470,7 +502,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     for (int cc = 0; cc < (ONECOL ? 1 : 2); ++cc) {
       const int m = 2 * t + cc;
       if (m >= a.M) continue;
-      if (a.epi == EPI_SILUMUL) {  // row g = gate, row g + 8 = up of the same output column
+      if (DUAL) {  // SwiGLU: row g = gate, row g + 8 = up of the same output column
         const int n = nbase + g;
         if (n < a.N[0]) {
           const float gt = bfround(v[cc]), up = bfround(v[2 + cc]);
@@ -493,7 +525,6 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
 
   // ---- main loop ---------------------------------------------------------------------------------------
   int run_start_kc = 0;  // k chunk at which this warp's share of the current tile began
-  bool pf_done = false;
   int tile = ub / upt, kc = ub - tile * upt;
   for (int u = ub; u < ue; ++u) {
     const int i = u - ub, st = i & 1;
@@ -503,91 +534,69 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
       for (int q = 0; q < 4; ++q) ys[q] = yb[q] = 0.f;
     }
     const bool tile_ends = kc == upt - 1 || u == ue - 1;
-    if (a.epi == EPI_RESADD && kc == upt - 1 && run_start_kc == 0) load_residual(tile);
-    mbar_wait_s(bar0 + st * 8, (i >> 1) & 1);
+    const uint32_t tok = mbar_wait_s(bar0 + st * 8, (i >> 1) & 1);
     const uint32_t wb = wst + st * kQ2WBytes, sb = sbst + st * kQ2SbBytes;
-    const uint4 sA = lds128(sb + g * 16), sB = lds128(sb + 128 + g * 16);
-    const uint32_t sAw[4] = {sA.x, sA.y, sA.z, sA.w}, sBw[4] = {sB.x, sB.y, sB.z, sB.w};
-    const uint32_t xg = x_lane + (uint32_t)kc * (8 * 128);
+    if (!(a.dbg & 1)) {
+      const uint32_t sp = sb + tok;
+      // two 128-byte chunks of every row, four groups each
 #pragma unroll
-    for (int jj = 0; jj < 8; ++jj) {
-      const int cch = jj >> 2, j = jj & 3;
-      const uint2 w0 = lds64(wb + cch * cs + woff[j]);
-      const uint2 w1 = lds64(wb + cch * cs + woff[j] + hs);
-      const uint4 x0 = lds128(xg + jj * 128), x1 = lds128(xg + jj * 128 + 16);
-      float acc[4];
-      if (ONECOL) {
-        const float n0 = __uint_as_float(lds32(nsx_lane + (uint32_t)(kc * 8 + jj) * 4));
-        acc[0] = acc[1] = acc[2] = acc[3] = n0;
-      } else {
-        const uint2 nn = lds64(nsx_lane + (uint32_t)(kc * 8 + jj) * 32);
-        acc[0] = acc[2] = __uint_as_float(nn.x);
-        acc[1] = acc[3] = __uint_as_float(nn.y);
-      }
-      const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+      for (int cch = 0; cch < 2; ++cch) {
+      const uint32_t wp = wb + tok + cch * cs;
+      const uint2 sA = lds64_t(sp + g * 16 + cch * 8, 0), sB = lds64_t(sp + 128 + g * 16 + cch * 8, 0);
+      const uint32_t sAw[2] = {sA.x, sA.y}, sBw[2] = {sB.x, sB.y};
+      const uint32_t xp = x_lane + (uint32_t)(kc * 8 + cch * 4) * 128 + tok;
+      const uint32_t np = nsx_lane + (uint32_t)(kc * 8 + cch * 4) * (ONECOL ? 16 : 64) + tok;
 #pragma unroll
-      for (int m = 0; m < 4; ++m) {
-        if (F16) {
-          const int sh = (m >> 1) * 8;
-          const uint32_t mk = (m & 1) ? lmask2 : lmask;
-          const uint32_t a0 = lift4b(w0.x, sh, mk, lmagic), a1 = lift4b(w1.x, sh, mk, lmagic),
-                         a2 = lift4b(w0.y, sh, mk, lmagic), a3 = lift4b(w1.y, sh, mk, lmagic);
-          mma_f16_16816(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1]);
-        } else {
-          const uint32_t a0 = lift4b(w0.x, 4 * m, lmask, lmagic), a1 = lift4b(w1.x, 4 * m, lmask, lmagic),
-                         a2 = lift4b(w0.y, 4 * m, lmask, lmagic), a3 = lift4b(w1.y, 4 * m, lmask, lmagic);
-          mma_bf16_16816(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1]);
+      for (int jj = 0; jj < 4; ++jj) {
+        const int j = jj;
+        const uint2 w0 = lds64_t(wp + woff[j], 0);
+        const uint2 w1 = lds64_t(wp + woff[j] + hs, 0);
+        // the accumulator's start value arrives as a register quad {n0, n1, n0, n1}: no moves in front of the first MMA
+        uint4 x0, x1, nq;
+        {  // (predicating these loads on the lanes that feed column 0 measured far slower: ptxas branches)
+          x0 = lds128_t(xp + jj * 128, 0); x1 = lds128_t(xp + jj * 128 + 16, 0);
+          nq = lds128_t(np + jj * (ONECOL ? 16 : 64), 0);
+        }
+        const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        float acc[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+          const int sh = F16 ? (m >> 1) * 8 : 4 * m;
+          const uint32_t mk = (F16 && (m & 1)) ? lmask2 : lmask;
+          uint32_t a0, a1, a2, a3;
+          {
+            a0 = lift4b(w0.x, sh, mk, lmagic); a1 = lift4b(w1.x, sh, mk, lmagic);
+            a2 = lift4b(w0.y, sh, mk, lmagic); a3 = lift4b(w1.y, sh, mk, lmagic);
+          }
+          if (m == 0) mma_16816<F16>(acc, a0, a1, a2, a3, xb[0], xb[1], __uint_as_float(nq.x), __uint_as_float(nq.y),
+                                     __uint_as_float(nq.z), __uint_as_float(nq.w));
+          else mma_16816<F16>(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1], acc[0], acc[1], acc[2], acc[3]);
+        }
+        const float s0 = jj & 1 ? bf16hi(sAw[jj >> 1]) : bf16lo(sAw[jj >> 1]);
+        const float s1 = jj & 1 ? bf16hi(sBw[jj >> 1]) : bf16lo(sBw[jj >> 1]);
+        ys[0] = fmaf(s0, acc[0], ys[0]);
+        ys[2] = fmaf(s1, acc[2], ys[2]);
+        if (!ONECOL) {
+          ys[1] = fmaf(s0, acc[1], ys[1]);
+          ys[3] = fmaf(s1, acc[3], ys[3]);
         }
       }
-      const float s0 = jj & 1 ? bf16hi(sAw[jj >> 1]) : bf16lo(sAw[jj >> 1]);
-      const float s1 = jj & 1 ? bf16hi(sBw[jj >> 1]) : bf16lo(sBw[jj >> 1]);
-      ys[0] = fmaf(s0, acc[0], ys[0]);
-      ys[2] = fmaf(s1, acc[2], ys[2]);
-      if (!ONECOL) {
-        ys[1] = fmaf(s0, acc[1], ys[1]);
-        ys[3] = fmaf(s1, acc[3], ys[3]);
       }
-    }
-    {  // bias term: biases (16 rows x 8 groups, as they lie in the stage) x the three pieces of sum_x
-      const uint32_t ba0 = lds32(sb + 256 + g * 16 + t * 4), ba1 = lds32(sb + 384 + g * 16 + t * 4);
+      {  // bias term: biases (16 rows x 8 groups, as they lie in the stage) x the three pieces of sum_x
+        const uint32_t ba0 = lds32_t(sp + 256 + g * 16 + t * 4, 0), ba1 = lds32_t(sp + 384 + g * 16 + t * 4, 0);
+        const uint32_t pp = pcs_lane + (uint32_t)kc * 16 + tok;
 #pragma unroll
-      for (int p = 0; p < 3; ++p) {
-        const uint32_t b0 = lds32(pcs_lane + (uint32_t)(p * COLS * gp + kc * 8) * 2);
-        mma_bf16_1688(yb, ba0, ba1, b0);
+        for (int p = 0; p < 3; ++p) {
+          const uint32_t b0 = lds32_t(pp + (uint32_t)p * COLS * gp * 2, 0);
+          mma_bf16_1688(yb, ba0, ba1, b0, yb);
+        }
       }
     }
     __syncwarp();
-    if (lane == 0 && p_u < ue) issue_next(st);
-    if (a.pf_on && !pf_done && u + 2 >= ue) {  // all own loads are out: ask L2 for this warp's first units of the next matrix
-      pf_done = true;
-      if (lane == 0) {
-        const int pG = gridDim.x;
-        const int ptl = (int)((long long)c * a.pf_ntiles / pG), pth = (int)((long long)(c + 1) * a.pf_ntiles / pG);
-        const int pcu = (pth - ptl) * a.pf_upt;
-        const int pb = ptl * a.pf_upt + (int)((long long)warp * pcu / kQ2Warps);
-        const int pe = ptl * a.pf_upt + (int)((long long)(warp + 1) * pcu / kQ2Warps);
-        int p0 = pb + a.pf_first, p1 = p0 + a.pf_count;
-        if (p1 > pe) p1 = pe;
-        for (int pu = p0; pu < p1; ++pu) {
-          const int ptile = pu / a.pf_upt, pkc = pu - ptile * a.pf_upt;
-          if (a.pf_dual) {
-            tma_prefetch_3d(&a.pf_wmap[0], 0, ptile * 8, 2 * pkc);
-            tma_prefetch_3d(&a.pf_wmap[1], 0, ptile * 8, 2 * pkc);
-            tma_prefetch_2d(&a.pf_smap[0], 8 * pkc, ptile * 8);
-            tma_prefetch_2d(&a.pf_smap[1], 8 * pkc, ptile * 8);
-            tma_prefetch_2d(&a.pf_bmap[0], 8 * pkc, ptile * 8);
-            tma_prefetch_2d(&a.pf_bmap[1], 8 * pkc, ptile * 8);
-          } else {
-            int si = 0;
-            if (a.pf_nseg > 1 && ptile >= a.pf_tile0[1]) si = 1;
-            if (a.pf_nseg > 2 && ptile >= a.pf_tile0[2]) si = 2;
-            const int r0 = (ptile - a.pf_tile0[si]) * 16;
-            tma_prefetch_3d(&a.pf_wmap[si], 0, r0, 2 * pkc);
-            tma_prefetch_2d(&a.pf_smap[si], 8 * pkc, r0);
-            tma_prefetch_2d(&a.pf_bmap[si], 8 * pkc, r0);
-          }
-        }
-      }
+    if (p_u < ue) {  // warp-uniform; one elected lane issues, every lane advances the cursor
+      if (elect_one()) issue(p_tile, p_kc, st);
+      ++p_u;
+      if (++p_kc == upt) { p_kc = 0; ++p_tile; }
     }
     const int kc_done = kc, tile_done = tile;
     if (++kc == upt) { kc = 0; ++tile; }
@@ -597,6 +606,9 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
 #pragma unroll
     for (int q = 0; q < 4; ++q) v[q] = F16 ? fmaf(ys[q], rs[q & 1], yb[q]) : ys[q] + yb[q];
     if (run_start_kc == 0 && kc_done == upt - 1) {
+      // (a whole tile inside one warp's run only happens for short-K, many-row matrices: the residual's L2 latency
+      // is paid here; the Llama o/down projections always finish through the cut-tile path below, which hides it)
+      if (a.epi == EPI_RESADD) load_residual(tile_done);
       epilogue(tile_done, v);
     } else if (e0_tile < 0) {
       // first partial share of this warp: parked in registers until the ring is idle
@@ -731,8 +743,7 @@ static bool fill_matrix(CUtensorMap* wmap, CUtensorMap* smap, CUtensorMap* bmap,
 }
 
 int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs,
-                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual,
-                    const pie_qmv_next* next) {
+                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual) {
   memset(&a, 0, sizeof(a));
   const int dual = epilogue == EPI_SILUMUL;
   if (!fill_matrix(a.wmap, a.smap, a.bmap, a.N, a.tile0, a.out_off, a.ntiles, segs, nseg, K, dual)) return PIE_EUNSUPPORTED;
@@ -741,24 +752,20 @@ int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld,
   a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
   a.out = (uint16_t*)out; a.out_ld = out_ld; a.residual = (const uint16_t*)residual; a.epi = epilogue;
   // fp16 staging of x (see q2_stage_x) needs every block of a thread in registers: M * kpad / 16 <= 4 * 512 blocks
-  static const int f16_env = getenv("PIE_QMV2_F16") ? atoi(getenv("PIE_QMV2_F16")) : 1;
-  a.f16 = f16_env && (long long)M * q2_kpad(K) / 16 <= 4 * kQ2Warps * 32;
+  static const int f16_env = getenv("PIE_QMV2_F16") ? atoi(getenv("PIE_QMV2_F16")) : -1;
+  // Measured on B200 (one row): fp16 staging wins where x is short (K = 4096: head 56 -> 51 us, gate/up equal), its extra
+  // reduction pass costs more than it saves at K = 14336 (down: 12.0 -> 12.5 us).  PIE_QMV2_F16 = 0 / 1 forces.
+  const bool f16_fits = (long long)M * q2_kpad(K) / 16 <= 4 * kQ2Warps * 32;
+  a.f16 = f16_fits && (f16_env < 0 ? (long long)M * K <= 8192 : f16_env != 0);
+  static const int dbg_env = getenv("PIE_QMV2_DBG") ? atoi(getenv("PIE_QMV2_DBG")) : 0;
+  a.dbg = dbg_env;
   a.lift_mask = 0x000f000fu; a.lift_mask2 = 0x00f000f0u; a.lift_magic = a.f16 ? 0x64006400u : 0x43004300u;
-  if (next && next->nseg > 0 && next->count > 0) {
-    const int ndual = next->dual;
-    int n_[kMaxSeg], off_[kMaxSeg];
-    if (next->K % kQ2UnitK == 0 &&
-        fill_matrix(a.pf_wmap, a.pf_smap, a.pf_bmap, n_, a.pf_tile0, off_, a.pf_ntiles, next->segs, next->nseg, next->K, ndual)) {
-      a.pf_on = 1; a.pf_nseg = next->nseg; a.pf_dual = ndual; a.pf_upt = q2_kpad(next->K) / kQ2UnitK;
-      a.pf_first = next->first; a.pf_count = next->count;
-    }
-  }
   return PIE_OK;
 }
 
-template <bool ONECOL, bool F16>
+template <bool ONECOL, bool F16, bool DUAL>
 static cudaError_t launch_qmv2_t(const Qmv2Args& a, bool pdl, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(qmv2_kernel<ONECOL, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQmvMaxSmem);
+  cudaError_t e = cudaFuncSetAttribute(qmv2_kernel<ONECOL, F16, DUAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQmvMaxSmem);
   if (e != cudaSuccess) return e;
   int grid = num_sms();
   if (grid > a.ntiles) grid = a.ntiles;
@@ -773,12 +780,16 @@ static cudaError_t launch_qmv2_t(const Qmv2Args& a, bool pdl, cudaStream_t st) {
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
   count_launch();
-  return cudaLaunchKernelEx(&cfg, qmv2_kernel<ONECOL, F16>, a);
+  return cudaLaunchKernelEx(&cfg, qmv2_kernel<ONECOL, F16, DUAL>, a);
+}
+template <bool ONECOL, bool F16>
+static cudaError_t launch_qmv2_d(const Qmv2Args& a, bool pdl, cudaStream_t st) {
+  return a.dual ? launch_qmv2_t<ONECOL, F16, true>(a, pdl, st) : launch_qmv2_t<ONECOL, F16, false>(a, pdl, st);
 }
 
 cudaError_t launch_qmv2(const Qmv2Args& a, bool pdl, cudaStream_t st) {
-  if (a.f16) return a.M == 1 ? launch_qmv2_t<true, true>(a, pdl, st) : launch_qmv2_t<false, true>(a, pdl, st);
-  return a.M == 1 ? launch_qmv2_t<true, false>(a, pdl, st) : launch_qmv2_t<false, false>(a, pdl, st);
+  if (a.f16) return a.M == 1 ? launch_qmv2_d<true, true>(a, pdl, st) : launch_qmv2_d<false, true>(a, pdl, st);
+  return a.M == 1 ? launch_qmv2_d<true, false>(a, pdl, st) : launch_qmv2_d<false, false>(a, pdl, st);
 }
 
 }  // namespace pie

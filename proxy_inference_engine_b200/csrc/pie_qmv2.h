@@ -16,11 +16,11 @@ constexpr int kQ2SbBytes = 512;    // bf16 scales (256 B) + biases (256 B) of a 
 
 struct Qmv2Args {
   CUtensorMap wmap[kMaxSeg], smap[kMaxSeg], bmap[kMaxSeg];           // this matrix (up to 3 row segments)
-  CUtensorMap pf_wmap[kMaxSeg], pf_smap[kMaxSeg], pf_bmap[kMaxSeg];  // the next matrix of the step (L2 prefetch)
   int N[kMaxSeg], tile0[kMaxSeg], out_off[kMaxSeg];
   int nseg, dual, M, K;
   int ntiles, upt;  // 16-row tiles (dual: 8 gate + 8 up rows); units per tile = ceil(K / 512)
   uint32_t lift_mask, lift_mask2, lift_magic;
+  int dbg;  // experiments (PIE_QMV2_DBG): 1 = skip the arithmetic, 2 = load weights only
   int f16;  // 1: activations staged as scaled fp16, weights lifted to fp16 (see q2_stage_x)
   const uint16_t* x;
   int x_ld;
@@ -30,15 +30,13 @@ struct Qmv2Args {
   int out_ld;
   const uint16_t* residual;
   int epi;
-  int pf_on, pf_nseg, pf_dual, pf_ntiles, pf_upt, pf_first, pf_count;
-  int pf_tile0[kMaxSeg];
 };
 
 size_t qmv2_smem_bytes(int M, int K);
 bool qmv2_supported(int M, int K, int bits, int group_size, const pie_qmv_seg* segs, int nseg, int dual);
 int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs,
-                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual,
-                    const pie_qmv_next* next);
+                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual);
 cudaError_t launch_qmv2(const Qmv2Args& a, bool pdl, cudaStream_t st);
+
 
 }  // namespace pie

@@ -126,6 +126,7 @@ class DecodeEngine:
             nb = max(nb, L.pie_qmv_workspace_bytes(mb, n, k, self.bits, dual, 0))
         self.qmv_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
         self.graph = None
+        self._next_pos = None
         self.launches_per_step = 0
         # fused=True: one cooperative launch per step (pie_decode_step), B <= 8.  Round-1 status: parity-green but
         # slower than the per-operator launches, hence opt-in
@@ -297,6 +298,7 @@ class DecodeEngine:
                 c.offset = 0
             logits = self.model(ids, cache=self.cache)
         self.positions.fill_(Lp - 1)
+        self._next_pos = Lp  # host-side mirror of the device positions: the cache slot the next step writes
         self.seq.zero_()
         self.seq[:, :Lp] = ids
         self.prompt_len = Lp
@@ -307,7 +309,15 @@ class DecodeEngine:
         return self.tokens
 
     def step(self, n: int = 1):
-        """n decode steps; each consumes self.tokens at self.positions and samples the next token."""
+        """n decode steps; each consumes self.tokens at self.positions and samples the next token.
+        The KV buffers hold max_context tokens: a step past that would write another row's (or page's) K/V, so it is
+        refused here (the reference grows its cache instead, reusable.py:167-203; this engine's buffers are fixed
+        because the captured graph holds their addresses)."""
+        if getattr(self, "_next_pos", None) is None:
+            raise ValueError("DecodeEngine.step() before prefill()")
+        if self._next_pos + n > self.max_context:
+            raise ValueError(f"decode step past max_context: position {self._next_pos} + {n} steps > {self.max_context}")
+        self._next_pos += n
         self._ensure_graph()
         for _ in range(n):
             if self.graph is not None:

@@ -19,7 +19,7 @@ ap2 = os.environ.get("PIE_PARTS", "")
 for skip in (tuple(ap2.split(";")) if ap2 else ("", "rope", "attn", "rope,attn", "rope,attn,o,qkv", "rope,attn,o,qkv,gu", "rope,attn,o,qkv,gu,down")):
     os.environ["PIE_DEBUG_SKIP"] = skip
     eng = dec.DecodeEngine(model, batch=a.batch, max_context=a.ctx + 200, attn_fused=False if a.unfused_attn else (True if a.fused_attn else None))
-    eng.positions.fill_(a.ctx); eng.tokens.fill_(5)
+    eng.positions.fill_(a.ctx); eng.tokens.fill_(5); eng._next_pos = a.ctx
     eng.step(3); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); eng.step(50); e1.record(); torch.cuda.synchronize()

@@ -15,7 +15,7 @@ over = {"num_hidden_layers": a.layers} if a.layers else {}
 margs = preset_args(a.model, bits=a.bits, **over)
 model = build_model(margs, random_weights(margs, seed=0, device="cuda"))
 eng = DecodeEngine(model, batch=a.batch, max_context=a.ctx + 200, trace=True)
-eng.positions.fill_(a.ctx); eng.tokens.fill_(5)
+eng.positions.fill_(a.ctx); eng.tokens.fill_(5); eng._next_pos = a.ctx
 eng.step(5); torch.cuda.synchronize()
 t = eng.step_trace.cpu().numpy().astype("int64")
 n = (len(t) - 4) // 2
