@@ -66,10 +66,14 @@ QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksp
   p.ks_w = ks_w;
   return p;
 }
+// Workspace layout shared by the GEMV (split-K) and the batched-decode GEMM: arrival counters live in a FIXED region at
+// the head of the buffer, partial sums and everything else behind it.  The kernels leave their counters at zero, so one
+// zero-initialised buffer serves any sequence of shapes -- which only holds because the counter region does not move
+// with the shape (a shape-dependent split let a later, larger matrix read an earlier matrix's partial sums as counters).
+constexpr size_t kWsCntBytes = 128 << 10;  // 32768 GEMV tiles (524288 weight rows)
 size_t qmv_ws_bytes(const QmvPlan& p) {
   if (p.ksplit <= 1) return 0;
-  const size_t cnt = (((size_t)p.ntiles * 4) + 255) & ~(size_t)255;
-  return cnt + (size_t)p.ntiles * p.ksplit * 128 * p.mt * sizeof(float);
+  return kWsCntBytes + (size_t)p.ntiles * p.ksplit * 128 * p.mt * sizeof(float);
 }
 
 // Validate one fused GEMV and fill its launch descriptor for activation rows m0 .. m0 + mb - 1 (mb <= kMaxBatch).
@@ -114,6 +118,7 @@ int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x,
   if (!dual) p.ntiles = tile;
   const size_t need = qmv_ws_bytes(p);
   if (need > workspace_bytes || (need && !workspace)) return PIE_EWORKSPACE;
+  if (need && (size_t)p.ntiles * 4 > kWsCntBytes) return PIE_EUNSUPPORTED;
   a.M = mb; a.ntiles = p.ntiles; a.ksplit = p.ksplit; a.kslice = p.kslice; a.ks_w = p.ks_w;
   a.ks_w_log2 = 0; while ((1 << a.ks_w_log2) < p.ks_w) ++a.ks_w_log2;
   a.nch = p.kslice / (stage_k(bits) * p.ks_w);
@@ -122,7 +127,7 @@ int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x,
   a.out = (uint16_t*)out + (size_t)m0 * out_ld;
   a.residual = residual ? (const uint16_t*)residual + (size_t)m0 * out_ld : nullptr;
   a.ws_cnt = (unsigned int*)workspace;
-  a.ws_part = (float*)((uint8_t*)workspace + ((((size_t)p.ntiles * 4) + 255) & ~(size_t)255));
+  a.ws_part = (float*)((uint8_t*)workspace + kWsCntBytes);
   return PIE_OK;
 }
 int status_of(cudaError_t e) { return cuda_status(e); }
@@ -130,7 +135,7 @@ int status_of(cudaError_t e) { return cuda_status(e); }
 // Workspace of the batched-decode GEMM, laid out so that it can share the buffer with the GEMV: the counter region
 // comes first and is as large as the GEMV's (both kernels leave their counters zero), then the normalised
 // activations, then the split-K partials.
-static inline size_t qmd_cnt_bytes(long long rows_total) { return ((size_t)(rows_total / 8 + 16) * 4 + 255) & ~(size_t)255; }
+static inline size_t qmd_cnt_bytes(long long) { return kWsCntBytes; }
 static size_t qmd_total_bytes(int M, long long rows_total, int K, int dual, int bits) {
   const int mb = M > kMaxBatch ? kMaxBatch : M;
   size_t worst = 0;

@@ -76,6 +76,22 @@ def test_quantized_matmul(env, bits, M, N, K):
     assert rel_l2(got, dense) < 6e-3
 
 
+@pytest.mark.parametrize("bits", [4, 8])
+def test_split_k_workspace_serves_any_sequence_of_shapes(env, bits):
+    """Regression: the split-K arrival counters sit in a FIXED region at the head of the caller's workspace.  With a
+    shape-dependent split, a larger matrix run after a smaller one on the same (zeroed-once) workspace read the smaller
+    one's partial sums as counters: 9..63 activation rows at Llama-8B widths were wrong from the second call on."""
+    orc, ops = env
+    for (M, N, K) in ((16, 1024, 4096), (16, 2048, 4096), (9, 4096, 4096), (32, 4096, 4096), (16, 4096, 2048),
+                      (40, 6144, 4096), (32, 2384, 4096), (16, 4096, 14336), (33, 1024, 4096)):
+        rng = np.random.default_rng(M + N + K)
+        wq, s, b = orc.quantize(_rand_w(rng, N, K), 64, bits)
+        x = orc.round_bf16(rng.standard_normal((M, K)).astype(np.float32))
+        ref = orc.quantized_matmul(x, wq, s, b, True, 64, bits, mode="B")
+        got = t2n(ops.quantized_matmul(n2t_bf16(x), n2t_words(wq), n2t_bf16(s), n2t_bf16(b), True, 64, bits))
+        assert rel_l2(got, ref) < 3e-3, (M, N, K, rel_l2(got, ref))
+
+
 # prefill sizes: M >= 64 runs on the tcgen05 / TMEM tile kernel (pie_qmm.cu): ragged M and N tiles, one and many K steps
 QMM_TC_CASES = [(64, 128, 128), (70, 64, 512), (128, 128, 256), (200, 384, 512), (256, 200, 1024), (300, 1024, 4096),
                 (1000, 264, 1152), (513, 4096, 2048), (96, 16, 14336)]
