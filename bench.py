@@ -54,17 +54,33 @@ def model_numbers(args, bits):
 
 
 # ------------------------------------------------------------------------------------------ CPU baseline
-def cpu_baseline(margs, bits, steps=1, warmup=0, budget_s=20.0):
+def host_threads():
+    """Threads the CPU arm uses: the cores this process may run on.  NOT omp_get_max_threads(): torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which made round 1's N>1 reference arms 15-20x slower than its N=1 arm."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_baseline(margs, bits, steps=1, warmup=0, budget_s=20.0, config1=True):
     """The reference's own `_qmm_t<float, bits, 64>` (MLX/mlx/backend/cpu/quantized.cpp:96-153, compiled where it lies
-    into oracle/_ref) on the decode shapes of this model, M = 1, row-sliced over the host's threads; falls back to
-    the oracle port when oracle/_ref is absent.  Sample: `n_layers_sample` transformer layers' seven matmuls;
-    tok/s extrapolated by parameter count (the path is a pure weight stream)."""
+    into oracle/_ref) on the decode shapes of this model, M = 1; falls back to the oracle port when oracle/_ref is
+    absent.  Reported figures (SURVEY 8d / BASELINE.md section 4):
+      value          all host cores (rows sliced over `cores` threads, each thread runs the untouched reference loop);
+      single_thread  1 thread -- MLX's CPU stream is one worker thread (MLX/mlx/scheduler.h:22-35) and `_qmm_t` has no
+                     intra-op threading: this is what the reference itself would do on this host;
+      bf16_exact     one matrix through `_qmm_t<bfloat16_t>` (what MLX-CPU really executes for a bf16 checkpoint on x86:
+                     every product and sum rounded to bf16 -- low precision, time only);
+      config1        BASELINE config 1 (Llama-3.2-1B q4, 128-token prefill, greedy decode) through the WHOLE oracle
+                     (attention, norms, rope, head), prefill and decode tok/s separately.
+    Sample: `n_layers_sample` transformer layers' seven matmuls, tok/s extrapolated by parameter count."""
     import numpy as np
     from oracle import oracle as orc
 
     R = orc.ref()
     kind = "reference" if R is not None else "port"
-    nthreads = (R.pie_ref_max_threads() if R is not None else orc.lib().orc_max_threads())
+    nthreads = host_threads()
     h, f = margs.hidden_size, margs.intermediate_size
     nh, nkv, d = margs.num_attention_heads, margs.num_key_value_heads, margs.head_dim
     shapes = [(nh * d, h), (nkv * d, h), (nkv * d, h), (h, nh * d), (f, h), (f, h), (h, f)]
@@ -77,35 +93,108 @@ def cpu_baseline(margs, bits, steps=1, warmup=0, budget_s=20.0):
         x = rng.standard_normal((1, k)).astype(np.float32)
         mats.append((n, k, wq, s, b, x, np.empty((1, n), np.float32)))
     layer_params = sum(n * k for n, k in shapes)
+    total_params = model_numbers(margs, bits)["params"]
 
-    def one_layer():
-        for n, k, wq, s, b, x, y in mats:
+    def one_layer(nt, only=None):
+        for i, (n, k, wq, s, b, x, y) in enumerate(mats):
+            if only is not None and i != only:
+                continue
             if R is not None:
                 R.pie_ref_qmm_t_f32_mt(y.reshape(-1), x.reshape(-1), wq.reshape(-1), s.reshape(-1), b.reshape(-1),
-                                       1, n, k, bits, 64, nthreads)
+                                       1, n, k, bits, 64, nt)
             else:
+                orc.lib().orc_set_threads(nt)
                 orc.lib().orc_qmm_t(y.reshape(-1), x.reshape(-1), wq.reshape(-1), s.reshape(-1), b.reshape(-1),
                                     1, n, k, bits, 64, 0)
 
-    t0 = time.perf_counter(); one_layer(); t_probe = time.perf_counter() - t0
+    t0 = time.perf_counter(); one_layer(nthreads); t_probe = time.perf_counter() - t0
     n_layers_sample = max(1, min(margs.num_hidden_layers, int(budget_s / max(t_probe, 1e-3) / max(steps + warmup, 1))))
     for _ in range(warmup):
         for _ in range(n_layers_sample):
-            one_layer()
+            one_layer(nthreads)
     times = []
     for _ in range(max(steps, 1)):
         t0 = time.perf_counter()
         for _ in range(n_layers_sample):
-            one_layer()
+            one_layer(nthreads)
         times.append(time.perf_counter() - t0)
     t_step = sum(times) / len(times)
-    total_params = model_numbers(margs, bits)["params"]
-    tok_s = 1.0 / (t_step * total_params / (layer_params * n_layers_sample))
-    return {"value": tok_s, "unit": "tok/s", "cores": int(nthreads), "kind": kind,
-            "sample": f"{n_layers_sample} transformer layer(s) x 7 quantized matmuls at M=1 (fp32 _qmm_t, "
-                      f"{layer_params * n_layers_sample / 1e6:.0f} M params of {total_params / 1e6:.0f} M), "
-                      f"extrapolated by parameter count; {t_step:.3f} s per sample",
-            "ms_per_step": t_step * 1e3 * total_params / (layer_params * n_layers_sample)}
+    scale = total_params / (layer_params * n_layers_sample)
+    out = {"value": 1.0 / (t_step * scale), "unit": "tok/s", "cores": int(nthreads), "kind": kind,
+           "sample": f"{n_layers_sample} transformer layer(s) x 7 quantized matmuls at M=1 (fp32 _qmm_t, "
+                     f"{layer_params * n_layers_sample / 1e6:.0f} M params of {total_params / 1e6:.0f} M), "
+                     f"extrapolated by parameter count; {t_step:.3f} s per sample; threads pinned to the process's "
+                     f"CPU affinity ({nthreads}), OMP_NUM_THREADS ignored",
+           "ms_per_step": t_step * 1e3 * scale}
+    # the reference's own threading: one worker thread (one layer's q_proj + gate_proj, scaled by parameter count)
+    t0 = time.perf_counter(); one_layer(1, only=0); one_layer(1, only=4); t1 = time.perf_counter() - t0
+    p1 = shapes[0][0] * shapes[0][1] + shapes[4][0] * shapes[4][1]
+    out["single_thread"] = {"value": 1.0 / (t1 * total_params / p1), "unit": "tok/s", "cores": 1,
+                            "sample": f"q_proj + gate_proj of one layer ({p1 / 1e6:.0f} M params), {t1:.3f} s"}
+    if R is not None:  # reference-exact bf16 arithmetic of MLX-CPU on x86 (low precision; time only)
+        n, k, wq = shapes[0][0], shapes[0][1], mats[0][2]
+        s16 = orc.to_bf16_bits(mats[0][3]); b16 = orc.to_bf16_bits(mats[0][4]); x16 = orc.to_bf16_bits(mats[0][5])
+        y16 = np.empty((1, n), np.uint16)
+        t0 = time.perf_counter()
+        R.pie_ref_qmm_t_bf16_mt(y16.reshape(-1), x16.reshape(-1), wq.reshape(-1), s16.reshape(-1), b16.reshape(-1),
+                                1, n, k, bits, 64, 1)
+        tb = time.perf_counter() - t0
+        t0 = time.perf_counter(); one_layer(1, only=0); tf = time.perf_counter() - t0
+        out["bf16_exact"] = {"value": 1.0 / (tb * total_params / (n * k)), "unit": "tok/s", "cores": 1,
+                             "slower_than_f32": round(tb / tf, 2), "precision": "low (bf16 accumulate), time only",
+                             "sample": f"q_proj {n}x{k}, _qmm_t<bfloat16_t,{bits},64>, {tb:.3f} s"}
+    if config1:
+        try:
+            out["config1"] = cpu_config1(nthreads)
+        except Exception as e:  # the whole-oracle leg must never cost the bench its line
+            out["config1"] = {"error": repr(e)[:200]}
+    return out
+
+
+def cpu_config1(nthreads, prompt_len=128, decode_steps=3):
+    """BASELINE config 1 through the whole CPU oracle (fp32 mode A = MLX-CPU on fp32 inputs): Llama-3.2-1B q4 gs64,
+    bs1, 128-token prompt in ONE forward (inference_engine.py:278), then greedy decode steps.  Random packed weights
+    (the path is data-independent).  Bounded: the prefill plus `decode_steps` steps."""
+    import numpy as np
+    from oracle import oracle as orc
+    from proxy_inference_engine_b200.checkpoint import LLAMA_PRESETS
+    cfg = dict(LLAMA_PRESETS["llama-3.2-1b"], rms_norm_eps=1e-5, rope_theta=500000.0, max_position_embeddings=131072,
+               quantization={"group_size": 64, "bits": 4})
+    oargs = orc.ModelArgs(**{k: v for k, v in cfg.items() if k in orc.ModelArgs.__dataclass_fields__})
+    rng = np.random.default_rng(1)
+    h, f, V = oargs.hidden_size, oargs.intermediate_size, oargs.vocab_size
+    nh, nkv, d = oargs.num_attention_heads, oargs.num_key_value_heads, oargs.head_dim
+
+    def lin(n, k):
+        return (rng.integers(0, 2**32, (n, k // 8), dtype=np.uint32),
+                (rng.random((n, k // 64), dtype=np.float32) * 0.02 / np.sqrt(k)).astype(np.float32),
+                (rng.random((n, k // 64), dtype=np.float32) * -0.15 / np.sqrt(k)).astype(np.float32))
+
+    w = {}
+    def put(name, n, k):
+        w[name + ".weight"], w[name + ".scales"], w[name + ".biases"] = lin(n, k)
+    put("model.embed_tokens", V, h)
+    for i in range(oargs.num_hidden_layers):
+        p = f"model.layers.{i}"
+        put(p + ".self_attn.q_proj", nh * d, h); put(p + ".self_attn.k_proj", nkv * d, h)
+        put(p + ".self_attn.v_proj", nkv * d, h); put(p + ".self_attn.o_proj", h, nh * d)
+        put(p + ".mlp.gate_proj", f, h); put(p + ".mlp.up_proj", f, h); put(p + ".mlp.down_proj", h, f)
+        w[p + ".input_layernorm.weight"] = np.ones(h, np.float32)
+        w[p + ".post_attention_layernorm.weight"] = np.ones(h, np.float32)
+    w["model.norm.weight"] = np.ones(h, np.float32)
+    orc.lib().orc_set_threads(nthreads)
+    o = orc.LlamaOracle(oargs, w, mode="A")
+    cache = o.make_cache()
+    ids = rng.integers(0, V, (1, prompt_len), dtype=np.int32)
+    t0 = time.perf_counter(); lg = o(ids, cache, last_only=True); t_pre = time.perf_counter() - t0
+    tok = int(lg[0, -1].argmax())
+    t0 = time.perf_counter()
+    for _ in range(decode_steps):
+        lg = o(np.array([[tok]], np.int32), cache); tok = int(lg[0, -1].argmax())
+    t_dec = (time.perf_counter() - t0) / decode_steps
+    return {"workload": "llama-3.2-1b q4 gs64 bs1, whole oracle (fp32 inside every op), prompt 128",
+            "prefill_tok_s": round(prompt_len / t_pre, 2), "decode_tok_s": round(1.0 / t_dec, 3), "cores": int(nthreads),
+            "sample": f"one 128-token prefill ({t_pre:.2f} s) + {decode_steps} decode steps ({t_dec:.3f} s each)"}
 
 
 class ClockSampler:
@@ -423,7 +512,7 @@ def run_reference(a):
     from proxy_inference_engine_b200.checkpoint import preset_args
     margs = preset_args(a.model, bits=a.bits)
     steps, warm = min(a.steps, 4), min(a.warmup, 1)
-    cb = cpu_baseline(margs, a.bits, steps=steps, warmup=warm, budget_s=60.0)
+    cb = cpu_baseline(margs, a.bits, steps=steps, warmup=warm, budget_s=60.0, config1=False)
     line = {"impl": "reference", "metric": "decode tok/s", "value": round(cb["value"], 4), "unit": "tok/s",
             "n_gpus": world, "steps": steps, "warmup": warm, "ms_per_step": round(cb["ms_per_step"], 2),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
