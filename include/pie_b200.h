@@ -167,6 +167,29 @@ int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_
                int32_t* seq_out, int seq_ld, void* stream);
 
 
+/* ---- (e) tensor-parallel exchange steps, one-shot over NVLink peer memory ----------------------------------------
+ * Replace the collectives of MLX's sharded linears at decode sizes: `all_sum` after a row-split matrix
+ * (QuantizedShardedToAllLinear, MLX/python/mlx/nn/layers/distributed.py:459-566) and the gather of vocabulary-split
+ * logits.  Every rank owns one SYMMETRIC buffer of pie_tp_buffer_bytes() bytes, zeroed once, mapped into every peer
+ * (CUDA IPC / fabric handles, e.g. torch.distributed._symmetric_memory); base[r] is rank r's buffer as mapped in THIS
+ * process.  `epoch`: 8 local device bytes holding {1, 0} initially; the kernels advance it themselves, so the calls can
+ * be captured in a CUDA graph and replayed.  All ranks must issue the same sequence of exchanges.
+ *   pie_tp_allreduce: out[rows, width] = bf16(residual + bf16(sum over ranks of partial)), fp32 sum in rank order
+ *                     (identical bits on every rank); rows * width <= max_elems and <= 131072.
+ *   pie_tp_allgather: every rank's slice [rows, width] lands at columns [rank * width, (rank + 1) * width) of the
+ *                     [rows, world * width] bf16 matrix at byte offset pie_tp_gather_offset() of EVERY rank's buffer. */
+typedef struct pie_tp_peers {
+  void* base[8];
+  int rank, world, max_elems;
+  void* epoch;
+} pie_tp_peers;
+size_t pie_tp_buffer_bytes(int world, int max_elems, size_t gather_bytes);
+size_t pie_tp_gather_offset(int world, int max_elems);
+int pie_tp_allreduce(void* out, const void* partial, const void* residual, int rows, int width,
+                     const pie_tp_peers* peers_host, void* stream);
+int pie_tp_allgather(const void* slice, int rows, int width, const pie_tp_peers* peers_host, void* stream);
+
+
 /* ---- a12  one whole decode step (L == 1) in ONE cooperative launch ---------------------------------------
  * Model.__call__ for a single new token per sequence (PIE/models/llama/language.py:199-210 -> LlamaModel.__call__
  * :170-187 -> TransformerBlock.__call__ :144-154 -> Attention.__call__ :75-108 / MLP.__call__ :126-127) followed by

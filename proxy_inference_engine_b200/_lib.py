@@ -29,6 +29,12 @@ class KvLayout(C.Structure):
                 ("page_table", C.c_void_p), ("pt_stride", C.c_int), ("page_size", C.c_int)]
 
 
+class TpPeers(C.Structure):
+    """pie_tp_peers"""
+    _fields_ = [("base", C.c_void_p * 8), ("rank", C.c_int), ("world", C.c_int), ("max_elems", C.c_int),
+                ("epoch", C.c_void_p)]
+
+
 class StepLayer(C.Structure):
     """pie_step_layer"""
     _fields_ = [("q", QmvSeg), ("k", QmvSeg), ("v", QmvSeg), ("o", QmvSeg), ("gate", QmvSeg), ("up", QmvSeg),
@@ -80,6 +86,10 @@ SIGNATURES = {
     "pie_silu_mul": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_add": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_argmax": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
+    "pie_tp_buffer_bytes": (_sz, [_i, _i, _sz]),
+    "pie_tp_gather_offset": (_sz, [_i, _i]),
+    "pie_tp_allreduce": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(TpPeers), _vp]),
+    "pie_tp_allgather": (_i, [_vp, _i, _i, C.POINTER(TpPeers), _vp]),
     "pie_decode_step_plan_bytes": (_sz, [_i]),
     "pie_decode_step_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_step_attn_ws_bytes": (_sz, [_i, _i, _i, _i]),

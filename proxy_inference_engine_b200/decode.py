@@ -69,6 +69,19 @@ class DecodeEngine:
             w = self.tp.world
             self.logits_local = torch.empty((B, a.vocab_size // w), dtype=bf, device=dev)
             self.logits_gather = torch.empty((w * B, a.vocab_size // w), dtype=bf, device=dev)  # rank-major rows
+            # exchange steps: one-shot pushes over NVLink peer memory (tp.TPExchange, csrc/pie_comm.cu) unless
+            # PIE_TP_ONESHOT=0 or symmetric memory cannot be set up (then NCCL collectives, as in round 1)
+            self.xch = None
+            self.part = torch.empty((B, h), dtype=bf, device=dev)
+            if os.environ.get("PIE_TP_ONESHOT", "1") != "0" and B * h <= 131072:
+                try:
+                    from .tp import TPExchange
+                    self.xch = TPExchange(self.tp, B * h, B, a.vocab_size // w, dev)
+                    self.logits = self.xch.gathered   # peers write their vocabulary slices straight into it
+                except Exception as e:  # pragma: no cover - depends on the box
+                    import warnings
+                    warnings.warn(f"one-shot tensor-parallel exchange unavailable ({e!r}); using NCCL collectives")
+                    self.xch = None
         # caches
         self.paged = paged
         if paged:
@@ -183,6 +196,12 @@ class DecodeEngine:
         Tensor parallel: rank 0 folds the residual into its partial sum, the others store theirs, and ONE all-reduce
         over [B, hidden] leaves the new residual stream on every rank (the exchange step of
         QuantizedShardedToAllLinear, MLX/python/mlx/nn/layers/distributed.py:459-566)."""
+        if self.tp_on and self.xch is not None:
+            # every rank stores its bare partial sums; the exchange adds them in rank order and THEN the residual
+            # (the order of MLX's sharded linear + TransformerBlock: all_sum first, h + r after)
+            self._qmv(self.part, hid, x, K, K, segs, 1, None, EPI_STORE, None)
+            self.xch.all_reduce(h, self.part, h, _stream())
+            return
         if not self.tp_on or self.tp.rank == 0:
             self._qmv(h, hid, x, K, K, segs, 1, None, EPI_RESADD, h)
         else:
@@ -233,6 +252,11 @@ class DecodeEngine:
         if self.tp_on:
             nl = self.logits_local.shape[1]
             self._qmv(self.logits_local, nl, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+            if self.xch is not None:
+                self.xch.all_gather(self.logits_local, _stream())
+                _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
+                                        _p(self.seq), self.seq.shape[1], _stream()), "argmax")
+                return
             dist.all_gather_into_tensor(self.logits_gather, self.logits_local, group=self.tp.group)
             self.logits.view(self.B, self.tp.world, nl).copy_(
                 self.logits_gather.view(self.tp.world, self.B, nl).permute(1, 0, 2))

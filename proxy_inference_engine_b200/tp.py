@@ -97,3 +97,54 @@ def all_gather_last(x: torch.Tensor, tp: TPInfo) -> torch.Tensor:
     dist.all_gather_into_tensor(out, x2, group=tp.group)
     out = out.view(tp.world, x2.shape[0], x2.shape[1]).permute(1, 0, 2)
     return out.reshape(*x.shape[:-1], tp.world * x.shape[-1])
+
+
+class TPExchange:
+    """One-shot exchanges over NVLink peer memory for the decode step (csrc/pie_comm.cu): every rank pushes its partial
+    row into a slot of every peer's SYMMETRIC buffer and reduces the `world` slots locally -- one small kernel per
+    exchange instead of an NCCL collective (8-16 KB messages are pure latency: ~11 us per ncclAllReduce at 2 GPUs,
+    ~26 us at 8, measured in round 1).  NCCL / torch.distributed stay for the rendezvous and for the prefill path.
+    The buffer comes from torch.distributed._symmetric_memory (CUDA IPC / fabric handles mapped into every peer)."""
+
+    def __init__(self, tp: TPInfo, max_elems: int, gather_rows: int, gather_width: int, device):
+        import ctypes as C
+
+        import torch.distributed._symmetric_memory as symm
+
+        from . import _lib
+        self.L = _lib.load()
+        self.tp = tp
+        self.max_elems = int(max_elems)
+        gbytes = gather_rows * gather_width * tp.world * 2
+        nbytes = self.L.pie_tp_buffer_bytes(tp.world, self.max_elems, gbytes)
+        group = tp.group if tp.group is not None else dist.group.WORLD
+        self.buf = symm.empty(int(nbytes), dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.epoch = torch.tensor([1, 0], dtype=torch.int32, device=device)
+        self.peers = _lib.TpPeers()
+        for r, ptr in enumerate(self.hdl.buffer_ptrs):
+            self.peers.base[r] = ptr
+        self.peers.rank, self.peers.world, self.peers.max_elems = tp.rank, tp.world, self.max_elems
+        self.peers.epoch = self.epoch.data_ptr()
+        goff = self.L.pie_tp_gather_offset(tp.world, self.max_elems)
+        self.gathered = self.buf[goff:goff + gbytes].view(torch.bfloat16).view(gather_rows, gather_width * tp.world)
+        self._C = C
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)  # every rank's buffer is zeroed before anyone pushes into it
+
+    def all_reduce(self, out, partial, residual, stream):
+        """out = bf16(residual + bf16(sum over ranks of partial)); partial [rows, width] bf16."""
+        from . import _lib
+        rows, width = partial.shape
+        _lib.check(self.L.pie_tp_allreduce(out.data_ptr(), partial.data_ptr(),
+                                           residual.data_ptr() if residual is not None else None, rows, width,
+                                           self._C.byref(self.peers), stream), "tp_allreduce")
+
+    def all_gather(self, slice_, stream):
+        """Every rank's [rows, width] slice -> self.gathered [rows, world * width] on every rank."""
+        from . import _lib
+        rows, width = slice_.shape
+        _lib.check(self.L.pie_tp_allgather(slice_.data_ptr(), rows, width, self._C.byref(self.peers), stream),
+                   "tp_allgather")
+        return self.gathered
