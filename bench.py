@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--paged", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--no-70b", action="store_true", help="N > 1: skip the Llama-3.1-70B tensor-parallel sub-records")
     ap.add_argument("--no-prefill", action="store_true", help="skip the prefill GEMM figure (BASELINE config 4 shapes)")
     return ap.parse_args()
 
@@ -307,6 +308,71 @@ def time_qmv_in_graph(eng, replays=20):
     return e0.elapsed_time(e1) * 1e-3 / replays, n
 
 
+def time_exchanges_in_graph(eng, replays=20):
+    """Tensor parallel only: a CUDA graph holding exactly one step's exchange steps (2 all-reduces per layer + the
+    gather of the logits), replayed between two CUDA events; every rank takes part.  Returns (seconds per step's
+    exchanges, count)."""
+    import torch
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        n = eng.enqueue_exchanges()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        eng.enqueue_exchanges()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(replays):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / replays, n
+
+
+def tp_subrecord(model_name, bits, batches, rank, world, prompt=128, steps=32):
+    """north_star's tensor-parallel curve: Llama-3.1-70B q4 at bs1 and bs16 on this many GPUs (BASELINE config 5).
+    One sharded random-init model (every rank draws the full tensors with the same seed and keeps its slice), one
+    engine per batch size; device-timed like the headline value (barrier, CUDA events, max over ranks)."""
+    import torch
+    import torch.distributed as dist
+    from proxy_inference_engine_b200 import tp as T
+    from proxy_inference_engine_b200.checkpoint import build_model, preset_args, random_weights
+    from proxy_inference_engine_b200.decode import DecodeEngine
+    margs = preset_args(model_name, bits=bits)
+    weights = random_weights(margs, seed=0, device="cuda", shard=(rank, world))
+    model = build_model(T.shard_args(margs, world), weights).set_tp(T.TPInfo(rank, world))
+    del weights
+    nums = model_numbers(margs, bits)
+    peak, _ = measured_peaks()
+    out = {}
+    for B in batches:
+        eng = DecodeEngine(model, batch=B, max_context=prompt + steps + 72)
+        ids = torch.randint(0, margs.vocab_size, (B, prompt), generator=torch.Generator().manual_seed(1))
+        eng.prefill(ids)
+        eng.step(4)
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); eng.step(steps); e1.record()
+        torch.cuda.synchronize(); dist.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0]) / steps
+        xs, xn = time_exchanges_in_graph(eng)
+        step_bytes = nums["weight_bytes"] + B * ((prompt + 4 + steps / 2) * nums["kv_bytes_per_ctx_token"])
+        out[f"bs{B}"] = {"tok_s": round(B / (ms * 1e-3), 2), "ms_per_step": round(ms, 4), "steps": steps,
+                         "hbm_frac_per_gpu": round(step_bytes / world / (ms * 1e-3) / 1e9 / peak, 4),
+                         "exchange_us_per_step": round(xs * 1e6, 1), "exchanges_per_step": xn,
+                         "exchange": "one-shot NVLink push" if eng.xch is not None else "NCCL"}
+        del eng
+        torch.cuda.empty_cache()
+    return {"workload": f"{model_name} random-init MLX q{bits} gs64, tp{world}, prompt {prompt}", **out}
+
+
 def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
     """dram__bytes_read.sum + dram__bytes_write.sum of the GEMV per launch, from the committed `ncu --set full` capture
     (profiles/r01e_prof_qmv_ncu_full_summary.csv: the q4 gate+up, down, qkv and o launches of one 8B layer).  The capture
@@ -398,6 +464,23 @@ def run_b200(a):
     # every rank takes part: the eager pass contains the tensor-parallel collectives
     qsec, nlaunch = (0.0, 0) if a.no_kernel_timing else time_qmv_launches(eng)
     gsec, gl = (0.0, 0) if a.no_kernel_timing else time_qmv_in_graph(eng)
+    xsec, xn, oneshot = 0.0, 0, False
+    sub70 = None
+    if world > 1:
+        xsec, xn = time_exchanges_in_graph(eng)
+        oneshot = eng.xch is not None
+        if not a.no_70b and a.model == "llama-3.1-8b":
+            launches_per_step = eng.launches_per_step
+            del eng, model
+            torch.cuda.empty_cache()
+            try:
+                sub70 = tp_subrecord("llama-3.1-70b", 4, (1, 16), rank, world)
+            except Exception as e:  # the sub-record must never cost the headline its line
+                sub70 = {"error": repr(e)[:300]}
+
+            class _E:  # what the line below still needs of the engine
+                pass
+            eng = _E(); eng.launches_per_step = launches_per_step
     if rank != 0:
         _finish(world)
         return
@@ -415,7 +498,8 @@ def run_b200(a):
         "config": {"workload": f"{a.model} random-init MLX q{a.bits} gs64, bs{B} greedy decode, prompt {a.prompt}, "
                                f"context {ctx0}..{ctx0 + a.steps}" + (", paged KV" if a.paged else ""),
                    "parallelism": "single GPU" if world == 1 else
-                   f"tp{world}: heads / ffn / vocab sharded, 2 NCCL all-reduces per layer + 1 all-gather of logits",
+                   f"tp{world}: heads / ffn / vocab sharded, 2 all-reduces per layer + 1 all-gather of logits, "
+                   + ("one-shot pushes over NVLink peer memory (pie_comm.cu)" if oneshot else "NCCL"),
                    "l2": "each step streams the whole weight set (>> 126 MB L2), no flush needed",
                    "layers": margs.num_hidden_layers},
         "e2e": {"value": round(B * a.steps / (e2e_ms * 1e-3), 2), "unit": "tok/s",
@@ -426,6 +510,15 @@ def run_b200(a):
                           "achieved_GBps_per_gpu": round(step_bytes / world / (ms / a.steps) / 1e6, 1),
                           "frac": round(step_bytes / world / (ms / a.steps) / 1e6 / peak, 4)},
     }
+    if world > 1:
+        h = margs.hidden_size
+        sent = (world - 1) * (2 * margs.num_hidden_layers * B * h * 2 + B * margs.vocab_size // world * 2)
+        line["tp_exchange"] = {"kind": "one-shot NVLink push" if oneshot else "NCCL", "exchanges_per_step": xn,
+                               "allreduce_us_per_step": round(xsec * 1e6, 1), "us_per_exchange": round(xsec * 1e6 / max(xn, 1), 2),
+                               "nvlink_bytes_sent_per_step_per_gpu": int(sent),
+                               "how": "CUDA graph of one step's exchanges alone, 20 replays between CUDA events"}
+        if sub70 is not None:
+            line["llama_3_1_70b_q4"] = sub70
     if a.layers:
         line["invalid"] = "layer count overridden (debug run)"
     if not a.no_kernel_timing:
@@ -433,7 +526,7 @@ def run_b200(a):
         ach = qbytes / gsec / 1e9      # in the step's own conditions: graph replay, dependent launch, back to back
         ach_eager = qbytes / qsec / 1e9
         traffic, traffic_src = ncu_traffic_per_launch(qbytes / nlaunch, a.bits)
-        line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}>", "achieved": round(ach, 1), "peak": peak,
+        line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}> + qmv2_kernel (TMA) on the wide matrices", "achieved": round(ach, 1), "peak": peak,
                             "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": traffic,
                             "traffic_source": traffic_src,
                             "launches_per_step": gl, "avg_launch_us": round(gsec / gl * 1e6, 2),

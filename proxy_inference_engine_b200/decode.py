@@ -280,6 +280,23 @@ class DecodeEngine:
         self._qmv(out, out.shape[1], h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
         return 4 * len(m.layers) + 1
 
+    def enqueue_exchanges(self):
+        """Only the tensor-parallel exchange steps of one decode step (2 per layer + the logits gather): bench.py times a
+        CUDA graph of these (the data exchanged is scratch).  Returns how many."""
+        n = 0
+        for _ in self.model.layers:
+            for _ in range(2):
+                if self.xch is not None:
+                    self.xch.all_reduce(self.part, self.part, None, _stream())
+                else:
+                    dist.all_reduce(self.part, op=dist.ReduceOp.SUM, group=self.tp.group)
+                n += 1
+        if self.xch is not None:
+            self.xch.all_gather(self.logits_local, _stream())
+        else:
+            dist.all_gather_into_tensor(self.logits_gather, self.logits_local, group=self.tp.group)
+        return n + 1
+
     def _ensure_graph(self):
         if not self.use_graph or self.graph is not None:
             return
