@@ -379,7 +379,10 @@ def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
     holds four of the five shapes, so the measured traffic / algorithmic ratio of those launches scales this run's
     average launch.  None if the capture is absent or was taken at another bit width."""
     import csv
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01e_prof_qmv_ncu_full_summary.csv")
+    pdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles")
+    path = os.path.join(pdir, "r02_prof_qmv_ncu_full_summary.csv")   # this round's capture (both GEMV kernels)
+    if not os.path.exists(path):
+        path = os.path.join(pdir, "r01e_prof_qmv_ncu_full_summary.csv")
     if bits != 4 or not os.path.exists(path):
         return None, "no ncu capture for this configuration"
     rows = {r[0]: r for r in csv.reader(open(path)) if r}
@@ -391,7 +394,8 @@ def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
         return None, "ncu summary not readable"
     alg = 66.10e6 + 33.07e6 + 14.18e6 + 9.45e6  # weights + scales + biases of gate+up, down, qkv, o
     ratio = (rd + wr) / alg
-    return int(alg_bytes_per_launch * ratio), f"ncu --set full capture of 4 launches (traffic / algorithmic = {ratio:.4f})"
+    return int(alg_bytes_per_launch * ratio), (f"{os.path.basename(path)}: committed ncu --set full capture of the step's GEMV "
+                                                f"launches (traffic / algorithmic = {ratio:.4f}); NOT measured in this run")
 
 
 def run_b200(a):
