@@ -197,9 +197,11 @@ int pie_tp_allgather(const void* slice, int rows, int width, const pie_tp_peers*
  *   h = embed[tokens]; per layer: qkv = qmv(rms_norm(h)); rope(q,k) at positions[b]; append k,v; flash-decode;
  *   h += qmv(attn; o); act = silu(gate)*up of qmv(rms_norm(h)); h += qmv(act; down);  logits = qmv(rms_norm(h); head);
  *   tokens[b] = argmax(logits[b]); positions[b] += 1; seq[b, positions[b]] = tokens[b].
- * A persistent kernel (one CTA per SM) walks the step's matrices in order: each warp keeps its cp.async weight ring
- * streaming across the grid barriers that separate the matrices, so HBM never idles between them.  Same arithmetic,
- * operation for operation, as the per-operator entry points above.  B <= 8 rows.
+ * A persistent kernel (one CTA per SM) walks the step's matrices in order: each warp's TMA weight ring goes on with the
+ * next matrix's units across the grid barriers that separate the matrices, so HBM never idles between them.  The GEMV
+ * arithmetic is that of the TMA-fed per-operator kernel (fp16 staging); attention, embedding and sampler as the
+ * per-operator entry points above.  Built for B == 1 and 4-bit weights with K % 512 == 0 (PIE_EUNSUPPORTED otherwise:
+ * use the per-operator calls).
  * Protocol: pie_decode_step_plan() (host only, no CUDA call) turns the description into `plan_host`
  * (pie_decode_step_plan_bytes(n_layers) bytes); the caller copies it to the device once; pie_decode_step() launches.
  * `sync_ws`: 256 device bytes, zeroed once at allocation.  attn_ws: pie_decode_step_attn_ws_bytes(), zeroed once. */
@@ -227,8 +229,9 @@ typedef struct pie_step_io {
   void *h, *qkv, *attn, *act, *logits;   /* bf16 scratch: [B,hidden] [B,(Hq+2Hkv)D] [B,Hq*D] [B,ffn] [B,vocab] */
   void* attn_ws; size_t attn_ws_bytes; int nsplit;  /* nsplit from pie_decode_step_pick_splits */
   void* qmv_ws; size_t qmv_ws_bytes;     /* split-K workspace of pie_qmv_fused (max over the step's matrices) */
-  unsigned long long* trace;             /* optional profiling aid: u64 [2 + 2 * (4 n_layers + 1)] receiving CTA 0's
-                                            %globaltimer at kernel start, and per matrix: input ready / matrix done */
+  unsigned long long* trace;             /* optional profiling aid: u64 [2 + 3 * (4 n_layers + 1)] receiving CTA 0's
+                                            %globaltimer at kernel start / end, and per matrix: input ready / x staged /
+                                            matrix done */
 } pie_step_io;
 size_t pie_decode_step_plan_bytes(int n_layers);
 int pie_decode_step_pick_splits(int B, int Hq, int Hkv, int max_context);

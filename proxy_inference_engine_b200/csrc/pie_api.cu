@@ -213,15 +213,11 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
     const int st0 = build_qmv_args(a, p, out, out_ld, x, x_ld, m0, mb, K, segs, nseg, group_size, bits, norm_weight, eps,
                                    epilogue, residual, ksplit_hint, workspace, workspace_bytes, 0);
     if (st0 != PIE_OK) return st0;
-    // TMA-fed GEMV (pie_qmv2.cu): 4-bit weights, up to 8 rows, K a multiple of 512.  PIE_QMV2: 0 = never (the cp.async
-    // kernel below), 1 = where it measured faster on B200 at one row (us, cp.async / TMA: gate+up 18.9 / 18.1, down 13.1 /
-    // 12.0, head 64.2 / 51.3; the small q/k/v and o matrices are launch-latency bound and 0.1 - 1 us faster on the
-    // cp.async kernel, whose launch descriptor is a tenth of the size), 2 = wherever it is supported.
+    // TMA-fed GEMV (pie_qmv2.cu): 4-bit weights, up to 8 rows, K a multiple of 512 -- every matrix of a Llama decode
+    // step.  PIE_QMV2=0 keeps the cp.async kernel below (B200, 8B shapes, one row, us cp.async / TMA: q/k/v 7.8 / 7.7,
+    // o 5.5 / 5.3, gate+up 18.9 / 16.5, down 13.1 / 11.5, head 64.2 / 49.7).
     const int q2_mode = env_int("PIE_QMV2", 1);
-    long long q2_elems = 0;
-    for (int i = 0; i < nseg; ++i) q2_elems += (long long)segs[i].N * K;
-    if (M <= 8 && x_ld % 8 == 0 && q2_mode && (q2_mode == 2 || q2_elems >= (32LL << 20)) &&
-        qmv2_supported(mb, K, bits, group_size, segs, nseg, a.dual)) {
+    if (M <= 8 && x_ld % 8 == 0 && q2_mode && qmv2_supported(mb, K, bits, group_size, segs, nseg, a.dual)) {
       Qmv2Args a2;
       const int st1 = build_qmv2_args(a2, out, out_ld, x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue, residual);
       if (st1 == PIE_OK) {

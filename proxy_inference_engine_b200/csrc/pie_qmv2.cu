@@ -35,106 +35,9 @@
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
 #include "pie_qmv2.h"
+#include "pie_qmv2_dev.cuh"
 
 namespace pie {
-
-// ------------------------------------------------------------------------------------------- PTX helpers
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* map, uint32_t bar, int c0, int c1, int c2,
-                                            uint64_t pol) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(pol)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_b(uint32_t dst, const void* map, uint32_t bar, int c0, int c1, uint64_t pol) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(pol)
-      : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_init_s(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-// returns 0 through a value the compiler cannot see through (the loads of the stage are made to depend on it)
-__device__ __forceinline__ uint32_t mbar_wait_s(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0, ok = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (ok) break;
-    if (++spins > PIE_SPIN_LIMIT) __trap();
-  }
-  return ok - 1;
-}
-// D(16x8) = A(16x8, bf16, row) * B(8x8, bf16, col) + C: a0 (g, 2t..2t+1), a1 (g+8, 2t..), b0 (k 2t..2t+1, n g).
-// Not volatile, C separate from D: the compiler interleaves the independent accumulator chains of a unit.
-__device__ __forceinline__ void mma_bf16_1688(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0, const float (&c)[4]) {
-  asm("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%8,%9,%10};"
-      : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
-      : "r"(a0), "r"(a1), "r"(b0), "f"(c[0]), "f"(c[1]), "f"(c[2]), "f"(c[3]));
-}
-template <bool F16>
-__device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
-                                          uint32_t b1, float c0, float c1, float c2, float c3) {
-  if (F16)
-    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
-        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c0), "f"(c1), "f"(c2), "f"(c3));
-  else
-    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
-        : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
-        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(c0), "f"(c1), "f"(c2), "f"(c3));
-}
-// Shared-memory loads that the compiler may schedule freely AFTER the value `tok` exists (tok = 0, produced by the
-// mbarrier wait: nothing is hoisted above the wait; a later TMA issue is an asm volatile with a memory clobber).
-__device__ __forceinline__ uint2 lds64_t(uint32_t addr, uint32_t tok) {
-  uint2 v;
-  asm("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr + tok));
-  return v;
-}
-__device__ __forceinline__ uint4 lds128_t(uint32_t addr, uint32_t tok) {
-  uint4 v;
-  asm("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr + tok));
-  return v;
-}
-__device__ __forceinline__ uint32_t lds32_t(uint32_t addr, uint32_t tok) {
-  uint32_t v;
-  asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr + tok));
-  return v;
-}
-__device__ __forceinline__ uint32_t elect_one() {
-  uint32_t pred;
-  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
-  return pred;
-}
-__device__ __forceinline__ uint32_t lift4b(uint32_t w, int sh, uint32_t mask, uint32_t magic) {
-  uint32_t d;
-  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(w >> sh), "r"(mask), "r"(magic));
-  return d;
-}
-
-// ------------------------------------------------------------------------------------------- geometry
-// Dynamic shared memory (base aligned to 1024 B):
-//   [weight stages: warp w, stage s at (2 w + s) * 4096][scale/bias stages: (2 w + s) * 512: 256 B scales, 256 B biases]
-//   [mbarriers 32 x 8 B][edge tile ids 32 x 4 B][reduction scratch 1 KB][-128 * group sums of x][bias-side pieces of the
-//   group sums][x in fragment order]
-constexpr int kQ2SbOff = kQ2Warps * kQ2Stages * kQ2WBytes;               // 131072
-constexpr int kQ2BarOff = kQ2SbOff + kQ2Warps * kQ2Stages * kQ2SbBytes;  // + 16384
-constexpr int kQ2EdgeOff = kQ2BarOff + kQ2Warps * kQ2Stages * 8;
-constexpr int kQ2RedOff = kQ2EdgeOff + kQ2Warps * 2 * 4;
-constexpr int kQ2VarOff = kQ2RedOff + 1024;
-
-__host__ __device__ inline int q2_kpad(int K) { return (K + kQ2UnitK - 1) / kQ2UnitK * kQ2UnitK; }
-__host__ __device__ inline int q2_xrow_bytes(int K) { return q2_kpad(K) * 2 + 16; }
-__host__ __device__ inline int q2_gpitch(int K) { return q2_kpad(K) / kGroup + 8; }  // bf16 elements per pieces row
 
 size_t qmv2_smem_bytes(int M, int K) {
   const int cols = M == 1 ? 1 : 8;
@@ -142,234 +45,6 @@ size_t qmv2_smem_bytes(int M, int K) {
   const size_t pieces = ((size_t)3 * cols * q2_gpitch(K) * 2 + 15) & ~(size_t)15;
   const size_t xs = (size_t)M * q2_xrow_bytes(K);
   return 1024 /* alignment slack */ + kQ2VarOff + nsx + pieces + xs;
-}
-
-// ------------------------------------------------------------------------------------------- x staging
-// x (optionally RMS-normalised: mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111) -> shared memory in B-fragment order:
-// within every block of 16 k, position 4 m + 2 h + l holds k = m + 8 h + 4 l (what lane t of the MMA needs for step m).
-// Also per 64-element group: the accumulator's start value -OFF * sum(staged x) and sum(x) as three bf16 pieces.
-//
-// F16 = false: x is staged as the bf16 values themselves, weights lift to bf16 128 + q (OFF = 128).
-// F16 = true : x is staged as fp16 after an exact power-of-two scaling of the row (max |x| lands in [2^14, 2^15), so
-//   every element down to 2^-28 of the row maximum converts exactly; smaller ones keep subnormal precision and move the
-//   dot product by less than an fp32 rounding), weights lift to fp16 1024 + q or 1024 + 16 q (two nibble positions
-//   per 16-bit half without a shift; x at odd k is pre-divided by 16), OFF = 1024.  The row scale is undone when a tile
-//   is finished.  Everything the MMA sees is exact in fp32 either way.
-template <bool ONECOL, bool F16>
-__device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, float* red) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int NT = kQ2Warps * 32;
-  constexpr int COLS = ONECOL ? 1 : 8;
-  const int kpad = q2_kpad(a.K), G = kpad / kGroup, gp = q2_gpitch(a.K);
-  constexpr int NSXB = ONECOL ? 16 : 64;  // bytes of start values per group: quads {n[2t], n[2t+1], n[2t], n[2t+1]}, t = 0..3
-  float* nsx = reinterpret_cast<float*>(var);
-  uint16_t* pieces = reinterpret_cast<uint16_t*>(var + (size_t)G * NSXB);
-  uint8_t* xs = var + (size_t)G * NSXB + (((size_t)3 * COLS * gp * 2 + 15) & ~(size_t)15);
-  auto put_nsx = [&](int grp, int m, float v) {
-    if (ONECOL) {
-      *reinterpret_cast<float4*>(nsx + grp * 4) = make_float4(v, v, v, v);
-    } else {
-      float* q = nsx + grp * 16 + (m >> 1) * 4 + (m & 1);
-      q[0] = v; q[2] = v;
-    }
-  };
-  const int xrow = q2_xrow_bytes(a.K);
-  const int bpr = kpad / 16;           // 16-element blocks per row (multiple of 32)
-  const int total = a.M * bpr;
-  const int nits = (total + NT - 1) / NT;
-  const bool keep = nits <= 4;         // every block of this thread stays in registers between the passes
-  uint4 blk[4][2];
-  auto load_round = [&](int it0) {
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int idx = (it0 + u) * NT + tid;
-      blk[u][0] = blk[u][1] = make_uint4(0, 0, 0, 0);
-      if (idx < total) {
-        const int m = idx / bpr, b = idx - m * bpr;
-        if (b * 16 < a.K) {
-          const uint4* src = reinterpret_cast<const uint4*>(a.x + (size_t)m * a.x_ld + b * 16);
-          blk[u][0] = ldcg128(src); blk[u][1] = ldcg128(src + 1);
-        }
-      }
-    }
-  };
-  // Per-row reductions: entry e = (round, warp) holds the value of blocks [32 e, 32 e + 32), which lie in one row
-  // (bpr % 32 == 0), so row m owns the entries [m * epr, (m + 1) * epr).  Warp m reduces row m: fixed order.
-  const int epr = bpr / 32;
-  if (a.norm_w) {
-    for (int it0 = 0; it0 < nits; it0 += 4) {
-      load_round(it0);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (it0 + u >= nits) break;
-        const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
-                                blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
-        float ss = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { const float lo = bf16lo(w8[j]), hi = bf16hi(w8[j]); ss += lo * lo + hi * hi; }
-        ss = warp_sum(ss);
-        if (lane == 0) red[(it0 + u) * kQ2Warps + warp] = ss;
-      }
-    }
-    __syncthreads();
-    if (warp < a.M) {
-      float tot = 0.f;
-      for (int e = warp * epr + lane; e < (warp + 1) * epr; e += 32) tot += red[e];
-      tot = warp_sum(tot);
-      if (lane == 0) red[192 + warp] = 1.0f / sqrtf(tot / (float)a.K + a.eps);
-    }
-    __syncthreads();
-  }
-  // block u of this thread -> its 16 values (normalised when asked), as floats holding bf16 values
-  auto values = [&](int u, int m, int b, bool live, float (&v)[16]) {
-    const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
-                            blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(w8[j]); v[2 * j + 1] = bf16hi(w8[j]); }
-    if (a.norm_w && live) {
-      const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + b * 16);
-      const uint4 w0 = __ldg(wp), w1 = __ldg(wp + 1);
-      const uint32_t wu[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-      const float inv = red[192 + m];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        v[2 * j] = bfround(bfround(v[2 * j] * inv) * bf16lo(wu[j]));
-        v[2 * j + 1] = bfround(bfround(v[2 * j + 1] * inv) * bf16hi(wu[j]));
-      }
-    }
-  };
-  if (F16) {
-    // (host guarantees nits <= 4: the normalised blocks stay in registers, packed, while the row maxima are reduced)
-    if (!a.norm_w) load_round(0);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (u >= nits) break;
-      const int idx = u * NT + tid;
-      const bool ok = idx < total;
-      const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
-      float v[16];
-      values(u, m, b, ok && b * 16 < a.K, v);
-      float amax = 0.f;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) amax = fmaxf(amax, fabsf(v[j]));
-      blk[u][0] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-      blk[u][1] = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
-      amax = warp_max(amax);
-      if (lane == 0) red[u * kQ2Warps + warp] = amax;
-    }
-    __syncthreads();
-    if (warp < a.M) {
-      float mx = 0.f;
-      for (int e = warp * epr + lane; e < (warp + 1) * epr; e += 32) mx = fmaxf(mx, red[e]);
-      mx = warp_max(mx);
-      // scale = 2^(14 - floor(log2 mx)); 1 for a zero (or denormal / non-finite) row
-      const uint32_t ex = (__float_as_uint(mx) >> 23) & 0xffu;
-      const bool sane = ex >= 16 && ex < 255;
-      if (lane == 0) {
-        red[200 + warp] = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;   // scale
-        red[208 + warp] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;               // 1 / scale
-      }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (u >= nits) break;
-      const int idx = u * NT + tid;
-      const bool ok = idx < total;
-      const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
-      const uint32_t w8[8] = {blk[u][0].x, blk[u][0].y, blk[u][0].z, blk[u][0].w,
-                              blk[u][1].x, blk[u][1].y, blk[u][1].z, blk[u][1].w};
-      float v[16];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { v[2 * j] = bf16lo(w8[j]); v[2 * j + 1] = bf16hi(w8[j]); }
-      float s = 0.f;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) s += v[j];
-      const float sc = red[200 + m], sc16 = sc * 0.0625f;
-      // what the MMA will see: fp16(v * scale), odd k also / 16; its exact sum starts the accumulator
-      uint32_t h[8];  // h[j] = fp16 pair (k = 2j, 2j + 1)
-      float sh = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        __half2 hv = __floats2half2_rn(v[2 * j] * sc, v[2 * j + 1] * sc16);
-        h[j] = *reinterpret_cast<uint32_t*>(&hv);
-        const float2 back = __half22float2(hv);
-        sh += back.x + back.y;
-      }
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      sh += __shfl_xor_sync(0xffffffffu, sh, 1);
-      sh += __shfl_xor_sync(0xffffffffu, sh, 2);
-      if (ok) {
-        // position pair (4 mm + 2 hh, +1) holds k = (mm + 8 hh, mm + 8 hh + 4): halves of h[] regrouped by PRMT
-        uint32_t o[8];
-#pragma unroll
-        for (int mm = 0; mm < 4; ++mm) {
-#pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            const int k0 = mm + 8 * hh, k1 = k0 + 4;
-            const uint32_t lo16 = (k0 & 1) ? (h[k0 >> 1] >> 16) : (h[k0 >> 1] & 0xffffu);
-            const uint32_t hi16 = (k1 & 1) ? (h[k1 >> 1] >> 16) : (h[k1 >> 1] & 0xffffu);
-            o[2 * mm + hh] = lo16 | (hi16 << 16);
-          }
-        }
-        uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)m * xrow + b * 32);
-        dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-        dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-        if ((b & 3) == 0) {
-          const int grp = b >> 2;
-          put_nsx(grp, m, -1024.f * sh);
-          const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
-          pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
-          pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
-          pieces[(2 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(lo) >> 16);
-        }
-      }
-    }
-  } else {
-    for (int it0 = 0; it0 < nits; it0 += 4) {
-      if (!(keep && a.norm_w)) load_round(it0);
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (it0 + u >= nits) break;
-        const int idx = (it0 + u) * NT + tid;
-        const bool ok = idx < total;
-        const int m = ok ? idx / bpr : 0, b = ok ? idx - m * bpr : 0;
-        float v[16];
-        values(u, m, b, ok && b * 16 < a.K, v);
-        float s = 0.f;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) s += v[j];
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        if (ok) {
-          uint32_t o[8];
-#pragma unroll
-          for (int mm = 0; mm < 4; ++mm) {
-            o[2 * mm] = pack_bf16(v[mm], v[mm + 4]);
-            o[2 * mm + 1] = pack_bf16(v[mm + 8], v[mm + 12]);
-          }
-          uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)m * xrow + b * 32);
-          dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-          dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-          if ((b & 3) == 0) {
-            const int grp = b >> 2;
-            put_nsx(grp, m, -128.f * s);
-            const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
-            pieces[(0 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
-            pieces[(1 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(mid) >> 16);
-            pieces[(2 * COLS + m) * gp + grp] = (uint16_t)(__float_as_uint(lo) >> 16);
-          }
-        }
-      }
-    }
-  }
-  if (!ONECOL) {  // columns >= M of the MMA are never stored, but their start values must be finite
-    for (int i = tid; i < G * 8; i += NT)
-      if ((i & 7) >= a.M) put_nsx(i >> 3, i & 7, 0.f);
-    for (int i = tid; i < 3 * COLS * gp; i += NT)
-      if ((i / gp) % COLS >= a.M) pieces[i] = 0;
-  }
 }
 
 // ------------------------------------------------------------------------------------------- the kernel
@@ -753,12 +428,12 @@ int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld,
   a.out = (uint16_t*)out; a.out_ld = out_ld; a.residual = (const uint16_t*)residual; a.epi = epilogue;
   // fp16 staging of x (see q2_stage_x) needs every block of a thread in registers: M * kpad / 16 <= 4 * 512 blocks
   static const int f16_env = getenv("PIE_QMV2_F16") ? atoi(getenv("PIE_QMV2_F16")) : -1;
-  // Measured on B200 (one row): fp16 staging wins where x is short (K = 4096: head 56 -> 51 us, gate/up equal), its extra
-  // reduction pass costs more than it saves at K = 14336 (down: 12.0 -> 12.5 us).  PIE_QMV2_F16 = 0 / 1 forces.
+  // fp16 staging (see q2_stage_x) needs every block of a thread in registers.  Measured on B200, one row, us bf16 / fp16
+  // staging: q/k/v 8.0 / 7.7, gate+up 17.4 / 16.5, head 52.2 / 49.7 (inputs that are RMS-normalised on the way in: the scale
+  // comes out of the same reduction pass), o 5.3 / 5.7, down 11.5 / 11.6 (plain inputs: the row maximum is an extra pass).
+  // Default: fp16 exactly when the RMS norm is fused.  PIE_QMV2_F16 = 0 / 1 forces.
   const bool f16_fits = (long long)M * q2_kpad(K) / 16 <= 4 * kQ2Warps * 32;
-  a.f16 = f16_fits && (f16_env < 0 ? (long long)M * K <= 8192 : f16_env != 0);
-  static const int dbg_env = getenv("PIE_QMV2_DBG") ? atoi(getenv("PIE_QMV2_DBG")) : 0;
-  a.dbg = dbg_env;
+  a.f16 = f16_fits && (f16_env < 0 ? norm_weight != nullptr : f16_env != 0);
   a.lift_mask = 0x000f000fu; a.lift_mask2 = 0x00f000f0u; a.lift_magic = a.f16 ? 0x64006400u : 0x43004300u;
   return PIE_OK;
 }

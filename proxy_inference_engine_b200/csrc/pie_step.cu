@@ -6,15 +6,19 @@
 // temp == 0 sampler + `cache.offset += 1` of generate_step (PIE/engine/inference_engine.py:282-297).
 //
 // Why one kernel: at batch 1 a layer's matrices are 9..66 MB, i.e. 1.5..10 us of HBM time each, while a kernel
-// boundary costs ~5 us of drain + launch + pipeline ramp.  Here one CTA per SM walks the step's matrices in order
-// (5 per layer); every warp issues the first ring stages of the NEXT matrix before it enters the grid barrier that
-// ends the current one, so the weight stream never stops at a matrix boundary.  Between q/k/v and o_proj the same
-// CTAs run RoPE + KV append + split-K flash-decode attention (o_proj's weights are already in flight).
-// The GEMV itself is qmv_body (pie_qmv_body.cuh): identical arithmetic to the per-operator entry points.
+// boundary costs ~3-5 us of drain + launch + pipeline ramp.  Here one CTA per SM walks the step's matrices in order
+// (4 per layer + the head); every warp's TMA ring simply goes on with the NEXT matrix's units when the current
+// matrix's are all requested, so the weight stream crosses the grid barriers that separate the matrices.  Between
+// q/k/v and o_proj the same CTAs run RoPE + KV append + split-K flash-decode attention (o_proj's first units are
+// already in shared memory).  The GEMV arithmetic is that of pie_qmv2.cu (TMA-fed, fp16 staging, one row).
+// Built for batch 1, 4-bit weights, K a multiple of 512 (the Llama decode step); other shapes use the
+// per-operator launches.
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
-#include "pie_qmv_body.cuh"
+#include "pie_qmv2.h"
+#include "pie_qmv2_dev.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace pie {
@@ -22,7 +26,7 @@ namespace pie {
 enum StepPre : int { PRE_BARRIER = 0, PRE_EMBED = 1, PRE_ATTN = 2 };
 
 struct StepPhase {
-  QmvArgs q;
+  Qmv2Args q;   // holds the matrix's TMA tensor maps: the plan lives in global memory, 64-byte aligned
   int pre;
   int pad_;
   // PRE_ATTN: attention of this layer, between the q/k/v matrix and o_proj
@@ -54,16 +58,17 @@ struct StepArgs {
   int vocab;
   int32_t* seq;
   int seq_ld;
-  unsigned int* bar;  // [0] arrivals, [1] generation
+  unsigned int* bar;  // [0] arrivals, [1] generation (grid_barrier); [2] running arrivals, [3] departures (flat form)
+  int pf_cross;           // units of a later matrix a warp may request before the current matrix is done (0..2)
   unsigned long long* trace;
+  unsigned long long* trace_stage;  // optional: 4 stamps per matrix from inside the x staging
 };
 
-struct StepHeader {  // head of the host/device plan buffer
+struct alignas(64) StepHeader {  // head of the host/device plan buffer (the phases behind it hold CUtensorMaps)
   uint32_t magic, bits, grid, smem, onecol, nphases, plan_bytes, pad_;
   StepArgs args;  // args.phases is patched at launch
 };
 constexpr uint32_t kStepMagic = 0x50494553u;
-constexpr int kStepWarps = 16;
 
 // ---- grid-wide barrier: arrivals counter + generation word; leaves the counter at zero --------------------------
 __device__ __forceinline__ void grid_barrier(unsigned int* bar) {
@@ -79,6 +84,21 @@ __device__ __forceinline__ void grid_barrier(unsigned int* bar) {
       while (ld_acquire_gpu(bar + 1) == gen) {}
     }
     __threadfence();
+  }
+  __syncthreads();
+}
+
+// Flat form used by the one-launch step: one fire-and-forget arrival and one polled word.  The word counts arrivals and
+// is not reset between barriers: barrier number k (from 1) is passed when it reaches k * gridDim.x.  The last CTA to
+// leave the kernel zeroes it.
+__device__ __forceinline__ void grid_barrier_flat(unsigned int* cnt, unsigned int target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    red_release_gpu_add(cnt, 1u);
+    unsigned int spins = 0;
+    while ((int)(ld_acquire_gpu(cnt) - target) < 0) {
+      if (++spins > (1u << 26)) __trap();
+    }
   }
   __syncthreads();
 }
@@ -430,68 +450,310 @@ __global__ void __launch_bounds__(kAttnWarps * 32, 1) attn_fused_kernel(const __
   attn_phase<D, R, CLUSTER, kAttnWarps>(s, P, scratch, &s_flag);
 }
 
-// The main loop of one matrix of the step.  Not inlined and free of calls: it needs the whole register file.
-template <int BITS, bool ONECOL>
-__device__ __noinline__ void step_matrix(const QmvArgs& a, uint8_t* smem, bool reinit) {
-  qmv_body<BITS, 1, ONECOL, true, QMV_MAIN>(a, smem, reinit, [] {});
+// ---- the one-launch step: TMA-fed GEMV phases (the arithmetic of pie_qmv2.cu, one row, fp16 staging) ---------------
+// Shared memory (base aligned to 1024 B): [weight stages 16 x 2 x 4096][scale/bias stages 16 x 2 x 512][mbarriers]
+// [edge tile ids][edge values 16 x 2 x 16 f32][reduction scratch 1 KB][per-phase: start-value quads, sum_x pieces, x]
+// The attention phase's scratch aliases the per-phase region (x is restaged by every matrix).
+constexpr int kS2EdgeValOff = kQ2RedOff + 1024;
+constexpr int kS2VarOff = kS2EdgeValOff + kQ2Warps * 2 * 16 * 4;
+__host__ __device__ inline size_t s2_var_bytes(int K) {
+  return (size_t)(q2_kpad(K) / kGroup) * 16 + (((size_t)3 * q2_gpitch(K) * 2 + 15) & ~(size_t)15) + (size_t)q2_xrow_bytes(K);
 }
 
-template <int BITS, bool ONECOL>
-__global__ void __launch_bounds__(kStepWarps * 32, 1) decode_step_kernel(const __grid_constant__ StepArgs s) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(16) StepPhase ph[2];
+// this CTA's / warp's run of units of a matrix (same partition as qmv2_kernel)
+struct S2Run { int ub, ue, upt; };
+__device__ __forceinline__ S2Run s2_run_of(const Qmv2Args& a, int warp) {
+  const int G = gridDim.x, c = blockIdx.x;
+  const int ntiles = a.ntiles, upt = a.upt;
+  // (32-bit arithmetic: c * ntiles < 2^31 for any matrix the plan accepts)
+  const int tile_lo = (int)((unsigned)c * (unsigned)ntiles / (unsigned)G);
+  const int tile_hi = (int)((unsigned)(c + 1) * (unsigned)ntiles / (unsigned)G);
+  const int cu = (tile_hi - tile_lo) * upt;
+  S2Run r;
+  r.upt = upt;
+  r.ub = tile_lo * upt + (int)((unsigned)warp * (unsigned)cu / kQ2Warps);
+  r.ue = tile_lo * upt + (int)((unsigned)(warp + 1) * (unsigned)cu / kQ2Warps);
+  return r;
+}
+
+__global__ void __launch_bounds__(kQ2Warps * 32, 1) decode_step2_kernel(const __grid_constant__ StepArgs s) {
+  extern __shared__ uint8_t smem_raw[];
   __shared__ int s_flag;
-  static_assert(sizeof(StepPhase) % 4 == 0, "phase descriptors are copied word-wise");
-  constexpr int PHW = sizeof(StepPhase) / 4;
-  float* scratch = reinterpret_cast<float*>(smem + kQmvBarBytes +
-                                            (size_t)kStepWarps * kQmvStages * QmvGeom<BITS>::STAGE_BYTES);
-  for (int i = threadIdx.x; i < PHW; i += blockDim.x)
-    reinterpret_cast<uint32_t*>(&ph[0])[i] = __ldg(reinterpret_cast<const uint32_t*>(s.phases) + i);
+  // The descriptors of the current and the next matrix, copied from the plan one matrix ahead: every scalar the x
+  // staging and the main loop read comes from shared memory (from global memory each is a dependent L2 round trip in
+  // front of the matrix: measured 4.6 us of staging).  TMA itself takes the tensor maps from the plan in global memory.
+  __shared__ __align__(64) StepPhase ph[2];
+  static_assert(sizeof(StepPhase) % 16 == 0, "phase descriptors are copied 16 bytes at a time");
+  constexpr int PHV = sizeof(StepPhase) / 16;
+  auto fetch_phase = [&](int q) {
+    if (q < s.nphases)
+      for (int i = threadIdx.x; i < PHV; i += blockDim.x)
+        reinterpret_cast<uint4*>(&ph[q & 1])[i] = __ldg(reinterpret_cast<const uint4*>(s.phases + q) + i);
+  };
+  fetch_phase(0);
+  fetch_phase(1);
   __syncthreads();
-  const bool tracing = s.trace && blockIdx.x == 0 && threadIdx.x == 0;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int g = lane >> 2, t = lane & 3;
+  const uint32_t smem_s = smem_u32(smem);
+  const uint32_t wst = smem_s + (uint32_t)(warp * kQ2Stages) * kQ2WBytes;
+  const uint32_t sbst = smem_s + kQ2SbOff + (uint32_t)(warp * kQ2Stages) * kQ2SbBytes;
+  const uint32_t bar0 = smem_s + kQ2BarOff + (uint32_t)(warp * kQ2Stages) * 8;
+  int* edge_tile = reinterpret_cast<int*>(smem + kQ2EdgeOff);
+  float* edge_val = reinterpret_cast<float*>(smem + kS2EdgeValOff);   // [warp][2][16]
+  float* red = reinterpret_cast<float*>(smem + kQ2RedOff);
+  uint8_t* var = smem + kS2VarOff;
+  float* scratch = reinterpret_cast<float*>(var);
+  const uint64_t pol = l2_policy_evict_first();
+  const bool tracing = s.trace && blockIdx.x == 0 && tid == 0;
   if (tracing) s.trace[0] = globaltimer_ns();
+  // grid barriers: arrivals accumulate in bar[2] (zero at launch: the last CTA to leave the kernel resets it)
+  unsigned int bar_target = 0;
+  auto gbar = [&]() { bar_target += gridDim.x; grid_barrier_flat(s.bar + 2, bar_target); };
+
+  // (tile, k chunk) of matrix `a` -> TMA copies into stage st of this warp's ring
+  // d: the matrix's scalars (shared copy, or the plan itself for a matrix further ahead); a: the plan entry (maps)
+  auto issue = [&](const Qmv2Args& d, const Qmv2Args& a, int tile, int kc, int st) {
+    const uint32_t bar = bar0 + st * 8, wd = wst + st * kQ2WBytes, sd = sbst + st * kQ2SbBytes;
+    mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
+    if (d.dual) {
+      const int r0 = tile * 8;
+      tma_load_3d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, pol);
+      tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, pol);
+      tma_load_2d_b(sd, &a.smap[0], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 128, &a.smap[1], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 256, &a.bmap[0], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 384, &a.bmap[1], bar, 8 * kc, r0, pol);
+    } else {
+      int si = 0;
+      if (d.nseg > 1 && tile >= d.tile0[1]) si = 1;
+      if (d.nseg > 2 && tile >= d.tile0[2]) si = 2;
+      const int r0 = (tile - d.tile0[si]) * 16;
+      tma_load_3d(wd, &a.wmap[si], bar, 0, r0, 2 * kc, pol);
+      tma_load_2d_b(sd, &a.smap[si], bar, 8 * kc, r0, pol);
+      tma_load_2d_b(sd + 256, &a.bmap[si], bar, 8 * kc, r0, pol);
+    }
+  };
+  int cur_phase = 0;  // the matrix being consumed: ph[] holds cur_phase and cur_phase + 1
+  auto desc_of = [&](int q) -> const Qmv2Args& {
+    return (q == cur_phase || q == cur_phase + 1) ? ph[q & 1].q : s.phases[q].q;
+  };
+  // Producer cursor: the next unit to request, possibly of a LATER matrix than the one being consumed -- the ring keeps
+  // streaming across the grid barriers.  pp = its phase, [p_u, p_ue) the rest of this warp's run there.
+  int pp = 0, p_u, p_ue, p_tile, p_kc, p_upt;
+  auto cursor_to_phase = [&](int q) {
+    pp = q;
+    if (q < s.nphases) {
+      const S2Run r = s2_run_of(desc_of(q), warp);
+      p_u = r.ub; p_ue = r.ue; p_upt = r.upt;
+      p_tile = r.ub / r.upt; p_kc = r.ub - p_tile * r.upt;
+    } else {
+      p_u = p_ue = 0; p_tile = p_kc = 0; p_upt = 1;
+    }
+  };
+  unsigned int n_issued = 0, n_used = 0;   // units requested / consumed by this warp since the kernel began
+  // Keep the ring full (two units in flight or waiting), but let at most `s.pf_cross` units of a matrix LATER than the
+  // one being consumed (`cur`) go out: requests that are in flight while the grid barrier and the x staging make their
+  // round trips queue in front of them (measured: 21.8 MB in flight -> 6 us barriers, 4.7 us staging).
+  auto top_up = [&](int cur) {   // warp-uniform; one elected lane issues
+    while (n_issued - n_used < 2u) {
+      while (pp < s.nphases && p_u >= p_ue) cursor_to_phase(pp + 1);
+      if (pp >= s.nphases) return;
+      if (pp > cur) {
+        // units of later matrices already out = everything issued beyond the current matrix's own units
+        if ((int)(n_issued - n_used) >= s.pf_cross) return;
+      }
+      if (elect_one()) issue(desc_of(pp), s.phases[pp].q, p_tile, p_kc, (int)(n_issued & 1u));
+      ++n_issued;
+      ++p_u;
+      if (++p_kc == p_upt) { p_kc = 0; ++p_tile; }
+    }
+  };
+
+  if (lane == 0) {
+    mbar_init_s(bar0, 1);
+    mbar_init_s(bar0 + 8, 1);
+    fence_mbar_init();
+    fence_proxy_async();
+  }
+  __syncwarp();
+  cursor_to_phase(0);
+  top_up(s.nphases);   // the very first units: nothing is waiting for a round trip yet
+
   for (int p = 0; p < s.nphases; ++p) {
+    cur_phase = p;
     const StepPhase& P = ph[p & 1];
-    // this warp's first ring stages of matrix p go in flight before anything else
-    qmv_body<BITS, 1, ONECOL, true, QMV_PREFETCH>(P.q, smem, false, [] {});
-    // produce the matrix's input (embedding / attention) and wait for the rest of the grid
+    const Qmv2Args& a = P.q;
+    // ---- produce the matrix's input (embedding / attention), then wait for the whole grid ------------------------
     if (P.pre == PRE_EMBED) {
-      embed_phase(s, BITS);
+      embed_phase(s, 4);
     } else if (P.pre == PRE_ATTN) {
-      grid_barrier(s.bar);
+      gbar();
       if (s.D == 128) {
-        if (s.R == 2) attn_phase<128, 2, false, kStepWarps>(s, P, scratch, &s_flag);
-        else attn_phase<128, 1, false, kStepWarps>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<128, 2, false, kQ2Warps>(s, P, scratch, &s_flag);
+        else attn_phase<128, 1, false, kQ2Warps>(s, P, scratch, &s_flag);
       } else {
-        if (s.R == 2) attn_phase<64, 2, false, kStepWarps>(s, P, scratch, &s_flag);
-        else attn_phase<64, 1, false, kStepWarps>(s, P, scratch, &s_flag);
+        if (s.R == 2) attn_phase<64, 2, false, kQ2Warps>(s, P, scratch, &s_flag);
+        else attn_phase<64, 1, false, kQ2Warps>(s, P, scratch, &s_flag);
       }
     }
-    grid_barrier(s.bar);
-    if (tracing) s.trace[2 + 2 * p] = globaltimer_ns();
-    if (p + 1 < s.nphases)  // the slot's previous user (matrix p - 1) is behind every warp of this CTA
-      for (int i = threadIdx.x; i < PHW; i += blockDim.x)
-        reinterpret_cast<uint32_t*>(&ph[(p + 1) & 1])[i] = __ldg(reinterpret_cast<const uint32_t*>(s.phases + p + 1) + i);
-    step_matrix<BITS, ONECOL>(P.q, smem, p > 0);  // its x staging ends with a CTA barrier: publishes the descriptor
-    if (tracing) s.trace[3 + 2 * p] = globaltimer_ns();
+    gbar();
+    if (tracing) s.trace[2 + 3 * p] = globaltimer_ns();
+    if (lane == 0) { edge_tile[warp * 2] = -1; edge_tile[warp * 2 + 1] = -1; }
+    q2_stage_x<true, true>(a, var, red, tracing && s.trace_stage ? s.trace_stage + 4 * p : nullptr);
+    __syncthreads();
+    if (tracing) s.trace[3 + 3 * p] = globaltimer_ns();
+    top_up(p);
+
+    // ---- this warp's units of matrix p ---------------------------------------------------------------------------
+    const S2Run run = s2_run_of(a, warp);
+    const int ub = run.ub, ue = run.ue, upt = run.upt;
+    const int dual = a.dual, epi = a.epi;
+    const int gp = q2_gpitch(a.K);
+    const uint32_t nsx_s = smem_u32(var);
+    const uint32_t pcs_s = nsx_s + (uint32_t)(q2_kpad(a.K) / kGroup) * 16;
+    const uint32_t xs_s = pcs_s + (uint32_t)((3 * gp * 2 + 15) & ~15);
+    const uint32_t x_lane = xs_s + t * 32;
+    const uint32_t pcs_lane = pcs_s + 2 * t * 2;
+    const uint32_t hs = dual ? 2048u : 1024u, cs = dual ? 1024u : 2048u;
+    const uint32_t w_lane = g * 128 + t * 8, gx5 = (g & 3) << 5;
+    const uint32_t lmask = a.lift_mask, lmask2 = a.lift_mask2, lmagic = a.lift_magic;
+    const float rs = red[208];
+
+    auto seg_of = [&](int tile, int& si, int& nbase) {
+      si = 0;
+      if (dual) { nbase = tile * 8; return; }
+      if (a.nseg > 1 && tile >= a.tile0[1]) si = 1;
+      if (a.nseg > 2 && tile >= a.tile0[2]) si = 2;
+      nbase = (tile - a.tile0[si]) * 16;
+    };
+    // finished tile: lanes t == 0 hold row g (v0) and row g + 8 (v1)
+    auto epilogue = [&](int tile, float v0, float v1) {
+      if (t != 0) return;
+      int si, nbase;
+      seg_of(tile, si, nbase);
+      if (dual) {   // SwiGLU: row g = gate, row g + 8 = up of the same output column
+        const int n = nbase + g;
+        if (n < a.N[0]) {
+          const float gt = bfround(v0), up = bfround(v1);
+          const float sg = bfround(1.f / (1.f + expf(-gt)));
+          a.out[n] = f2bf(bfround(gt * sg) * up);
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int n = nbase + g + 8 * h;
+          if (n < a.N[si]) {
+            float r = bfround(h ? v1 : v0);
+            if (epi == EPI_RESADD) r = bf16lo((uint32_t)ldcg16(a.residual + a.out_off[si] + n)) + r;
+            a.out[a.out_off[si] + n] = f2bf(r);
+          }
+        }
+      }
+    };
+
+    float ys0 = 0.f, ys2 = 0.f, yb[4] = {0.f, 0.f, 0.f, 0.f};
+    int n_edges = 0, run_start_kc = 0;
+    int tile = ub / upt, kc = ub - tile * upt;
+    for (int u = ub; u < ue; ++u) {
+      const int st = n_used & 1;
+      if (u == ub || kc == 0) { run_start_kc = kc; ys0 = ys2 = 0.f; yb[0] = yb[1] = yb[2] = yb[3] = 0.f; }
+      const uint32_t tok = mbar_wait_s(bar0 + st * 8, (n_used >> 1) & 1);
+      {
+        const uint32_t wb = wst + st * kQ2WBytes + w_lane + tok, sp = sbst + st * kQ2SbBytes + tok;
+        const uint32_t xp = x_lane + (uint32_t)kc * (8 * 128) + tok;
+        const uint32_t np = nsx_s + (uint32_t)kc * 8 * 16 + tok;
+#pragma unroll
+        for (int cch = 0; cch < 2; ++cch) {
+          const uint2 sA = lds64_t(sp + g * 16 + cch * 8, 0), sB = lds64_t(sp + 128 + g * 16 + cch * 8, 0);
+          const uint32_t sAw[2] = {sA.x, sA.y}, sBw[2] = {sB.x, sB.y};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t wo = wb + cch * cs + ((uint32_t)(j << 5) ^ gx5);
+            const uint2 w0 = lds64_t(wo, 0), w1 = lds64_t(wo + hs, 0);
+            const uint4 x0 = lds128_t(xp + (cch * 4 + j) * 128, 0), x1 = lds128_t(xp + (cch * 4 + j) * 128 + 16, 0);
+            const uint4 nq = lds128_t(np + (cch * 4 + j) * 16, 0);
+            const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+            float acc[4];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+              const int sh = (m >> 1) * 8;
+              const uint32_t mk = (m & 1) ? lmask2 : lmask;
+              const uint32_t a0 = lift4b(w0.x, sh, mk, lmagic), a1 = lift4b(w1.x, sh, mk, lmagic),
+                             a2 = lift4b(w0.y, sh, mk, lmagic), a3 = lift4b(w1.y, sh, mk, lmagic);
+              if (m == 0) mma_16816<true>(acc, a0, a1, a2, a3, xb[0], xb[1], __uint_as_float(nq.x), __uint_as_float(nq.y),
+                                          __uint_as_float(nq.z), __uint_as_float(nq.w));
+              else mma_16816<true>(acc, a0, a1, a2, a3, xb[2 * m], xb[2 * m + 1], acc[0], acc[1], acc[2], acc[3]);
+            }
+            ys0 = fmaf(j & 1 ? bf16hi(sAw[j >> 1]) : bf16lo(sAw[j >> 1]), acc[0], ys0);
+            ys2 = fmaf(j & 1 ? bf16hi(sBw[j >> 1]) : bf16lo(sBw[j >> 1]), acc[2], ys2);
+          }
+        }
+        const uint32_t ba0 = lds32_t(sp + 256 + g * 16 + t * 4, 0), ba1 = lds32_t(sp + 384 + g * 16 + t * 4, 0);
+        const uint32_t pb = pcs_lane + (uint32_t)kc * 16 + tok;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) mma_bf16_1688(yb, ba0, ba1, lds32_t(pb + (uint32_t)q * gp * 2, 0), yb);
+      }
+      ++n_used;
+      __syncwarp();
+      top_up(p);
+      const int kc_done = kc, tile_done = tile;
+      if (++kc == upt) { kc = 0; ++tile; }
+      if (kc_done != upt - 1 && u != ue - 1) continue;
+      // ---- this warp's share of the tile is complete: lanes t == 0 hold rows g (v0) and g + 8 (v1) -----------------
+      const float v0 = fmaf(ys0, rs, yb[0]), v1 = fmaf(ys2, rs, yb[2]);
+      if (run_start_kc == 0 && kc_done == upt - 1) {
+        epilogue(tile_done, v0, v1);
+      } else {
+        if (t == 0) { edge_val[(warp * 2 + n_edges) * 16 + g] = v0; edge_val[(warp * 2 + n_edges) * 16 + 8 + g] = v1; }
+        if (lane == 0) edge_tile[warp * 2 + n_edges] = tile_done;
+        ++n_edges;
+      }
+    }
+    // the warp whose run holds a cut tile's LAST unit adds the tile's shares in warp (= k) order and finishes it
+    int fin_tile = -1;
+    {
+      const int first_tile = ub / upt;
+      if (ue > ub && ub > first_tile * upt && (first_tile + 1) * upt <= ue) fin_tile = first_tile;
+    }
+    __syncthreads();
+    if (fin_tile >= 0) {
+      float v0 = 0.f, v1 = 0.f;
+      for (int w2 = 0; w2 <= warp; ++w2) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          if (edge_tile[w2 * 2 + e] != fin_tile) continue;
+          v0 += edge_val[(w2 * 2 + e) * 16 + g];
+          v1 += edge_val[(w2 * 2 + e) * 16 + 8 + g];
+        }
+      }
+      epilogue(fin_tile, v0, v1);
+    }
+    if (tracing) s.trace[4 + 3 * p] = globaltimer_ns();
+    // every warp of this CTA is past matrix p (the barrier above): its descriptor slot takes matrix p + 2.  A warp's
+    // producer cursor may already sit in matrix p + 1 (its copy is in the other slot) but not beyond...
+    __syncthreads();
+    fetch_phase(p + 2);
   }
-  grid_barrier(s.bar);
+  gbar();
   if (tracing) s.trace[1] = globaltimer_ns();
   argmax_phase(s, scratch, reinterpret_cast<int*>(scratch + 32));
+  // every CTA is past the last barrier once it gets here: the last one to leave zeroes the counters for the next launch
+  if (tid == 0 && atomicAdd(s.bar + 3, 1u) == gridDim.x - 1) {
+    s.bar[2] = 0;
+    s.bar[3] = 0;
+    __threadfence();
+  }
 }
 
-template <int BITS, bool ONECOL>
-static cudaError_t launch_step_t(const StepArgs& s, int grid, size_t smem, cudaStream_t st) {
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(decode_step_kernel<BITS, ONECOL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kQmvMaxSmem - 2048);
-    if (e != cudaSuccess) return e;
-    configured = true;
-  }
+static cudaError_t launch_step2(const StepArgs& s, int grid, size_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(decode_step2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kQmvMaxSmem - 4096);
+  if (e != cudaSuccess) return e;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid, 1, 1);
-  cfg.blockDim = dim3(kStepWarps * 32, 1, 1);
+  cfg.blockDim = dim3(kQ2Warps * 32, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -500,7 +762,7 @@ static cudaError_t launch_step_t(const StepArgs& s, int grid, size_t smem, cudaS
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   count_launch();
-  return cudaLaunchKernelEx(&cfg, decode_step_kernel<BITS, ONECOL>, s);
+  return cudaLaunchKernelEx(&cfg, decode_step2_kernel, s);
 }
 
 }  // namespace pie
@@ -533,8 +795,8 @@ size_t pie_decode_step_attn_ws_bytes(int B, int Hq, int D, int nsplit) {
 int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, const pie_step_io* io, void* plan_host,
                          size_t plan_bytes) {
   if (!m || !layers || !io || !plan_host) return PIE_ENULL;
-  if (m->n_layers <= 0 || io->B <= 0 || io->B > 8) return PIE_EUNSUPPORTED;
-  if (m->group_size != 64 || (m->bits != 4 && m->bits != 8)) return PIE_EUNSUPPORTED;
+  if (m->n_layers <= 0 || io->B != 1) return PIE_EUNSUPPORTED;           // batch 1 (the latency-bound case)
+  if (m->group_size != 64 || m->bits != 4) return PIE_EUNSUPPORTED;       // 4-bit weights
   if (m->D != 64 && m->D != 128) return PIE_EUNSUPPORTED;
   if (m->Hq <= 0 || m->Hkv <= 0 || m->Hq % m->Hkv || m->hidden % 64 || m->ffn % 64) return PIE_EINVAL_SHAPE;
   if (plan_bytes < pie_decode_step_plan_bytes(m->n_layers)) return PIE_EWORKSPACE;
@@ -549,15 +811,16 @@ int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, 
   StepPhase* ph = reinterpret_cast<StepPhase*>(H + 1);
   size_t smem = 0;
   int np = 0;
+  int max_k = 0;
   auto add = [&](void* out, int out_ld, const void* x, int x_ld, int K, const pie_qmv_seg* segs, int nseg,
                  const void* norm, int epi, const void* residual, int pre) -> int {
-    QmvPlan pl;
     StepPhase& P = ph[np];
-    const int st = build_qmv_args(P.q, pl, out, out_ld, x, x_ld, 0, B, K, segs, nseg, m->group_size, m->bits, norm,
-                                  m->rms_eps, epi, residual, 0, io->qmv_ws, io->qmv_ws_bytes, kStepWarps);
+    if (!qmv2_supported(1, K, m->bits, m->group_size, segs, nseg, epi == PIE_EPI_SILUMUL)) return PIE_EUNSUPPORTED;
+    const int st = build_qmv2_args(P.q, out, out_ld, x, x_ld, 1, K, segs, nseg, norm, m->rms_eps, epi, residual);
     if (st != PIE_OK) return st;
-    const size_t need = qmv_smem_bytes(B, pl.kslice, m->bits, kStepWarps, 1) + (size_t)kStepWarps * 32 * kQmvProdWords * 4;
-    if (need > smem) smem = need;
+    // fp16 staging throughout the step (one arithmetic path in the kernel)
+    P.q.f16 = 1; P.q.lift_magic = 0x64006400u;
+    if (K > max_k) max_k = K;
     P.pre = pre;
     ++np;
     return PIE_OK;
@@ -593,12 +856,13 @@ int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, 
   const int n_rep = m->Hq / m->Hkv;
   // two query heads per unit: with 512 threads per CTA (128 registers each) four heads' fp32 accumulators spill
   const int R = n_rep % 2 == 0 ? 2 : 1;
-  // the attention phase borrows the shared memory behind the weight rings: 16 warps x R x (D + 2) floats
-  const size_t stage = m->bits == 4 ? QmvGeom<4>::STAGE_BYTES : QmvGeom<8>::STAGE_BYTES;
-  const size_t attn_need = kQmvBarBytes + (size_t)kStepWarps * kQmvStages * stage +
-                           (size_t)kStepWarps * R * (m->D + 2) * sizeof(float);
-  if (attn_need > smem) smem = attn_need;
-  if (smem > (size_t)kQmvMaxSmem - 2048) return PIE_EUNSUPPORTED;
+  // per-phase region: x, its start values and pieces for the widest K -- or the attention phase's scratch
+  // ((16 warps + 1) x R x (D + 2) floats), whichever is larger
+  size_t var = s2_var_bytes(max_k);
+  const size_t attn_need = (size_t)(kQ2Warps + 1) * R * (m->D + 2) * sizeof(float);
+  if (attn_need > var) var = attn_need;
+  smem = 1024 + kS2VarOff + var;
+  if (smem > (size_t)kQmvMaxSmem - 4096) return PIE_EUNSUPPORTED;  // the kernel also holds two descriptors statically
   H->magic = kStepMagic; H->bits = (uint32_t)m->bits; H->grid = (uint32_t)num_sms(); H->smem = (uint32_t)smem;
   H->onecol = B == 1; H->nphases = (uint32_t)np; H->plan_bytes = (uint32_t)plan_bytes;
   StepArgs& s = H->args;
@@ -611,6 +875,8 @@ int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, 
   s.e_wq = m->embed.wq; s.e_s = (const uint16_t*)m->embed.scales; s.e_b = (const uint16_t*)m->embed.biases;
   s.tokens = io->tokens; s.table_rows = m->embed.N; s.hidden = hid; s.h = (uint16_t*)io->h;
   s.trace = io->trace;
+  s.trace_stage = io->trace ? io->trace + 2 + 3 * (4 * m->n_layers + 1) + 2 : nullptr;  // behind the per-matrix stamps
+  { const char* e = getenv("PIE_STEP_PF"); s.pf_cross = e && *e ? atoi(e) : 1; if (s.pf_cross < 0) s.pf_cross = 0; if (s.pf_cross > 2) s.pf_cross = 2; }
   s.logits = (const uint16_t*)io->logits; s.vocab = m->vocab; s.seq = io->seq; s.seq_ld = io->seq_ld;
   return PIE_OK;
 }
@@ -684,10 +950,7 @@ int pie_decode_step(const void* plan_dev, const void* plan_host, size_t plan_byt
   s.phases = reinterpret_cast<const StepPhase*>(reinterpret_cast<const uint8_t*>(plan_dev) + sizeof(StepHeader));
   s.bar = reinterpret_cast<unsigned int*>(sync_ws);
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e;
-  if (H->bits == 4) e = H->onecol ? launch_step_t<4, true>(s, H->grid, H->smem, st) : launch_step_t<4, false>(s, H->grid, H->smem, st);
-  else e = H->onecol ? launch_step_t<8, true>(s, H->grid, H->smem, st) : launch_step_t<8, false>(s, H->grid, H->smem, st);
-  return status_of(e);
+  return status_of(launch_step2(s, H->grid, H->smem, st));
 }
 
 }  // extern "C"

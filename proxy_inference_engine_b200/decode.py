@@ -151,8 +151,8 @@ class DecodeEngine:
     def _plan_fused(self):
         """Describe the step to pie_decode_step_plan (host only) and upload the plan once."""
         a, m, L, B = self.args, self.model, self.L, self.B
-        if B > 8:
-            raise ValueError("the fused decode step serves B <= 8")
+        if B != 1 or self.bits != 4:
+            raise ValueError("the one-launch decode step serves batch 1 with 4-bit weights (the latency-bound case)")
 
         def seg(l):
             return QmvSeg(l.weight.data_ptr(), l.scales.data_ptr(), l.biases.data_ptr(), l.weight.shape[0])
@@ -174,7 +174,7 @@ class DecodeEngine:
         nb = L.pie_decode_step_attn_ws_bytes(B, self.Hq, self.D, self.step_nsplit)
         self.step_attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=self.dev)
         self.step_sync = torch.zeros(256, dtype=torch.uint8, device=self.dev)
-        self.step_trace = (torch.zeros(4 + 2 * (4 * len(m.layers) + 1), dtype=torch.int64, device=self.dev)
+        self.step_trace = (torch.zeros(4 + 7 * (4 * len(m.layers) + 1), dtype=torch.int64, device=self.dev)
                            if self.trace else None)
         io = StepIO(B, _p(self.tokens), _p(self.positions), _p(self.seq), self.seq.shape[1], _p(self.h), _p(self.qkv),
                     _p(self.attn), _p(self.act), _p(self.logits), _p(self.step_attn_ws), self.step_attn_ws.numel(),

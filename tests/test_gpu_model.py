@@ -43,8 +43,12 @@ def test_model_forward_matches_oracle_per_layer():
     (4, False, 64, 1, False, False),
 ])
 def test_decode_engine_parity(bits, tie, head_dim, batch, paged, graph, fused):
-    """fused=False: one launch per operator; fused=True: the whole step in one cooperative launch (pie_decode_step)."""
-    args = tiny_args(bits=bits, tie=tie, head_dim=head_dim)
+    """fused=False: one launch per operator; fused=True: the whole step in one cooperative launch (pie_decode_step:
+    batch 1, 4-bit weights, K a multiple of 512)."""
+    if fused and (batch != 1 or bits != 4):
+        pytest.skip("the one-launch step serves batch 1 with 4-bit weights")
+    kw = dict(hidden_size=512, intermediate_size=1024, num_attention_heads=512 // head_dim) if fused else {}
+    args = tiny_args(bits=bits, tie=tie, head_dim=head_dim, **kw)
     rep = run_decode_parity(args, prompt_len=20, steps=12, batch=batch, paged=paged, use_graph=graph, fused=fused)
     assert rep["max_rel_err"] < TOL, rep
     assert rep["strong_mismatch"] == 0, rep
@@ -54,17 +58,17 @@ def test_decode_engine_parity(bits, tie, head_dim, batch, paged, graph, fused):
 
 @pytest.mark.parametrize("bits,head_dim,batch,heads,kv_heads,ctx", [
     (4, 128, 1, 8, 2, 40),      # n_rep 4 (the 8B / 1B grouping)
-    (4, 128, 2, 8, 1, 300),     # n_rep 8 (the 70B grouping): two query-head groups per kv head, several splits
-    (8, 64, 8, 4, 4, 150),      # n_rep 1, full batch of the fused step
-    (4, 64, 5, 8, 4, 700),      # n_rep 2, long context: several rounds per warp
+    (4, 128, 1, 8, 1, 300),     # n_rep 8 (the 70B grouping): two query-head groups per kv head, several splits
+    (4, 64, 1, 8, 8, 150),      # n_rep 1
+    (4, 64, 1, 8, 4, 700),      # n_rep 2, long context: several rounds per warp
 ])
 def test_fused_step_matches_per_operator_path(bits, head_dim, batch, heads, kv_heads, ctx):
-    """pie_decode_step against the per-operator launches on the same engine state: same tokens, logits equal up to
-    the split-K merge order of attention (the GEMVs are the same code and bit-identical)."""
+    """pie_decode_step against the per-operator launches on the same engine state: same tokens up to near-ties, logits
+    equal up to fp32 summation order (attention split merge; cp.async vs TMA GEMV)."""
     from proxy_inference_engine_b200.checkpoint import build_model, random_weights
     from proxy_inference_engine_b200.decode import DecodeEngine
     args = tiny_args(bits=bits, head_dim=head_dim, num_attention_heads=heads, num_key_value_heads=kv_heads,
-                     hidden_size=heads * head_dim if heads * head_dim >= 256 else 256)
+                     hidden_size=max(512, heads * head_dim), intermediate_size=1024)
     model = build_model(args, random_weights(args, seed=7, device="cuda", gen_device="cpu"))
     prompt = torch.randint(0, args.vocab_size, (batch, ctx), generator=torch.Generator().manual_seed(11))
     outs = []
