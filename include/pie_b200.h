@@ -183,6 +183,21 @@ typedef struct pie_tp_peers {
   int rank, world, max_elems;
   void* epoch;
 } pie_tp_peers;
+/* The all-reduce FUSED into the matrices on either side of it (batch 1): mode 1 = producer -- the o / down projection
+ * stores its partial row straight into slot `rank` of every peer's buffer instead of `out`; mode 2 = consumer -- the
+ * next matrix's x load waits for the `world` flags and takes x = x + bf16(sum of the slots) (x = the residual stream),
+ * stores that new residual stream to h_out (which must not alias x) and goes on with its RMS norm.  No kernel of its own,
+ * no extra pass over the row.  A buffer used this way must not be used by pie_tp_allreduce / pie_tp_allgather (separate
+ * exchange numbers): give the fused path its own buffer and epoch (16 bytes: {1, 0, 0, 0}). */
+typedef struct pie_tp_fused {
+  pie_tp_peers peers;
+  int mode;      /* 0 none, 1 producer, 2 consumer */
+  void* h_out;   /* mode 2: bf16 [K], receives the new residual stream */
+} pie_tp_fused;
+int pie_qmv_fused_tp(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs_host,
+                     int nseg, int group_size, int bits, const void* norm_weight, float eps, int epilogue,
+                     const void* residual, int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl,
+                     const pie_tp_fused* tp_host, void* stream);
 size_t pie_tp_buffer_bytes(int world, int max_elems, size_t gather_bytes);
 size_t pie_tp_gather_offset(int world, int max_elems);
 int pie_tp_allreduce(void* out, const void* partial, const void* residual, int rows, int width,

@@ -35,6 +35,11 @@ class TpPeers(C.Structure):
                 ("epoch", C.c_void_p)]
 
 
+class TpFused(C.Structure):
+    """pie_tp_fused"""
+    _fields_ = [("peers", TpPeers), ("mode", C.c_int), ("h_out", C.c_void_p)]
+
+
 class StepLayer(C.Structure):
     """pie_step_layer"""
     _fields_ = [("q", QmvSeg), ("k", QmvSeg), ("v", QmvSeg), ("o", QmvSeg), ("gate", QmvSeg), ("up", QmvSeg),
@@ -86,6 +91,8 @@ SIGNATURES = {
     "pie_silu_mul": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_add": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_argmax": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i, _vp]),
+    "pie_qmv_fused_tp": (_i, [_vp, _i, _vp, _i, _i, _i, C.POINTER(QmvSeg), _i, _i, _i, _vp, _f, _i, _vp, _i, _vp,
+                              _sz, _i, C.POINTER(TpFused), _vp]),
     "pie_tp_buffer_bytes": (_sz, [_i, _i, _sz]),
     "pie_tp_gather_offset": (_sz, [_i, _i]),
     "pie_tp_allreduce": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(TpPeers), _vp]),

@@ -205,7 +205,16 @@ size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int du
 int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
                   int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
                   int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
+  return pie_qmv_fused_tp(out, out_ld, x, x_ld, M, K, segs, nseg, group_size, bits, norm_weight, eps, epilogue, residual,
+                          ksplit_hint, workspace, workspace_bytes, pdl, nullptr, stream);
+}
+
+int pie_qmv_fused_tp(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
+                     int group_size, int bits, const void* norm_weight, float eps, int epilogue, const void* residual,
+                     int ksplit_hint, void* workspace, size_t workspace_bytes, int pdl, const pie_tp_fused* tp,
+                     void* stream) {
   if (M == 0) return PIE_OK;
+  if (tp && !tp->mode) tp = nullptr;
   for (int m0 = 0; m0 < M; m0 += kMaxBatch) {
     const int mb = M - m0 < kMaxBatch ? M - m0 : kMaxBatch;
     QmvArgs a;
@@ -219,13 +228,15 @@ int pie_qmv_fused(void* out, int out_ld, const void* x, int x_ld, int M, int K, 
     const int q2_mode = env_int("PIE_QMV2", 1);
     if (M <= 8 && x_ld % 8 == 0 && q2_mode && qmv2_supported(mb, K, bits, group_size, segs, nseg, a.dual)) {
       Qmv2Args a2;
-      const int st1 = build_qmv2_args(a2, out, out_ld, x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue, residual);
+      const int st1 = build_qmv2_args(a2, out, out_ld, x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue, residual, tp);
       if (st1 == PIE_OK) {
         const int st2 = cuda_status(launch_qmv2(a2, pdl != 0, (cudaStream_t)stream));
         if (st2 != PIE_OK) return st2;
         continue;
       }
+      if (tp) return st1;
     }
+    if (tp) return PIE_EUNSUPPORTED;  // the fused exchange lives in the TMA GEMV (one row, 4-bit, K % 512 == 0)
     // Batched-decode GEMM on tcgen05 (pie_qmd.cu).  PIE_QMD: 0 never, 1 where it measured faster than the GEMV at 32
     // rows (B200, 8B shapes, us GEMV / tcgen05: q8 gate+up 121 / 98, q8 head 417 / 290, q4 head 233 / 217; the narrow
     // matrices and 4-bit gate+up / down are still faster on the GEMV: DESIGN.md section 4.6), 2 wherever it is supported.

@@ -20,8 +20,6 @@
 
 namespace pie {
 
-constexpr int kTpMaxWorld = 8;
-constexpr int kTpMaxCtas = 32;
 constexpr int kTpChunk = 4096;  // bf16 elements per CTA (512 threads x 16 B)
 
 struct TpArgs {
@@ -38,24 +36,6 @@ struct TpArgs {
   long long dst_off;
 };
 
-__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int e) {
-  unsigned long long spins = 0;
-  while ((int)(ld_acquire_sys(p) - e) < 0) {
-    if (++spins > 4096) __nanosleep(256);
-    if (spins > (1ull << 28)) __trap();  // ~ a minute: a peer died
-  }
-}
-__host__ __device__ inline size_t tp_flags_off(int world, int max_elems) {
-  return (((size_t)2 * world * max_elems * 2) + 255) & ~(size_t)255;
-}
 __device__ __forceinline__ void tp_depart(const TpArgs& a) {
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -55,6 +55,14 @@ struct QmvArgs {
   unsigned int* ws_cnt;  // [ntiles], zero before the first launch, self-cleaning
 };
 
+// tensor-parallel exchange buffers (pie_comm.cu, pie_qmv2.cu): data [2 sets][world][max_elems] bf16, then flags
+// [2 sets][world][kTpMaxCtas] u32
+constexpr int kTpMaxWorld = 8;
+constexpr int kTpMaxCtas = 32;
+__host__ __device__ inline size_t tp_flags_off(int world, int max_elems) {
+  return (((size_t)2 * world * max_elems * 2) + 255) & ~(size_t)255;
+}
+
 struct KvLayout {
   long long batch_stride, head_stride, tok_stride;
   const int32_t* page_table;

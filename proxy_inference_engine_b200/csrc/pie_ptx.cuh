@@ -130,6 +130,22 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// ------------------------------------------------------------------ system-scope flags (tensor-parallel exchanges)
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void wait_flag(const unsigned int* p, unsigned int e) {
+  unsigned long long spins = 0;
+  while ((int)(ld_acquire_sys(p) - e) < 0) {
+    if (++spins > 4096) __nanosleep(256);
+    if (spins > (1ull << 28)) __trap();  // ~ a minute: a peer died
+  }
+}
 // ------------------------------------------------------------------ cp.async (LDGSTS) per-thread copies
 __device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");

@@ -125,6 +125,8 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
   pdl_launch_dependents();
   pdl_wait();
+  unsigned int tp_e = 0, tp_set = 0;
+  if (ONECOL && a.tp_mode == 1) { tp_e = *reinterpret_cast<volatile unsigned int*>(a.tp_epoch); tp_set = tp_e & 1u; }
   q2_stage_x<ONECOL, F16>(a, var, red);
   __syncthreads();
 
@@ -173,6 +175,26 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   auto epilogue = [&](int tile, const float (&v)[4]) {
     int si, nbase;
     seg_of(tile, si, nbase);
+    if (ONECOL && a.tp_mode == 1) {
+      // fused exchange, producer: the tile's 16 partial sums (rows g in v[0], rows g + 8 in v[2] of the lanes t == 0) are
+      // gathered into lane 0 and go to every peer's slot as two 16-byte stores (2-byte stores over NVLink are slow)
+      const uint32_t lo = f2bf(v[0]), hi = f2bf(v[2]);
+      uint32_t w[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        w[i] = __shfl_sync(0xffffffffu, lo, 8 * i) | (__shfl_sync(0xffffffffu, lo, 8 * i + 4) << 16);
+        w[4 + i] = __shfl_sync(0xffffffffu, hi, 8 * i) | (__shfl_sync(0xffffffffu, hi, 8 * i + 4) << 16);
+      }
+      if (lane == 0) {
+        for (int p = 0; p < a.tp_world; ++p) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(a.tp_peer[p]) +
+                                                ((size_t)tp_set * a.tp_world + a.tp_rank) * a.tp_max_elems + a.out_off[si] + nbase);
+          dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+          dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+      }
+      return;
+    }
 #pragma unroll
     for (int cc = 0; cc < (ONECOL ? 1 : 2); ++cc) {
       const int m = 2 * t + cc;
@@ -322,6 +344,29 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     }
     epilogue(fin_tile, v);
   }
+  if (ONECOL && a.tp_mode == 1) {
+    // producer: when this rank's LAST CTA is done, every peer may read slot `tp_rank` of exchange tp_e
+    // (one fence by one thread behind the CTA barrier -- cumulative over the CTA's pushes -- not one per thread)
+    __syncthreads();
+    if (tid == 0) __threadfence_system();
+    if (tid == 0 && atomicAdd(&a.tp_epoch[2], 1u) == gridDim.x - 1) {
+      a.tp_epoch[2] = 0;   // (the release of the flag stores below is the only other fence: every CTA fenced its own pushes)
+      const size_t foff = tp_flags_off(a.tp_world, a.tp_max_elems);
+      for (int p = 0; p < a.tp_world; ++p)
+        st_release_sys(reinterpret_cast<unsigned int*>(a.tp_peer[p] + foff) + ((size_t)tp_set * a.tp_world + a.tp_rank) * kTpMaxCtas, tp_e);
+    }
+  } else if (ONECOL && a.tp_mode == 2) {
+    // consumer: the last CTA out advances the exchange number (every CTA read it in the x staging)
+    __syncthreads();
+    if (tid == 0) {
+      __threadfence();
+      if (atomicAdd(&a.tp_epoch[1], 1u) == gridDim.x - 1) {
+        a.tp_epoch[1] = 0;
+        __threadfence();
+        a.tp_epoch[0] += 1;
+      }
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------- host side
@@ -418,7 +463,8 @@ static bool fill_matrix(CUtensorMap* wmap, CUtensorMap* smap, CUtensorMap* bmap,
 }
 
 int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs,
-                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual) {
+                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual,
+                    const pie_tp_fused* tp) {
   memset(&a, 0, sizeof(a));
   const int dual = epilogue == EPI_SILUMUL;
   if (!fill_matrix(a.wmap, a.smap, a.bmap, a.N, a.tile0, a.out_off, a.ntiles, segs, nseg, K, dual)) return PIE_EUNSUPPORTED;
@@ -434,6 +480,20 @@ int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld,
   // Default: fp16 exactly when the RMS norm is fused.  PIE_QMV2_F16 = 0 / 1 forces.
   const bool f16_fits = (long long)M * q2_kpad(K) / 16 <= 4 * kQ2Warps * 32;
   a.f16 = f16_fits && (f16_env < 0 ? norm_weight != nullptr : f16_env != 0);
+  if (tp && tp->mode) {
+    const pie_tp_peers& pr = tp->peers;
+    if (M != 1 || pr.world < 1 || pr.world > kTpMaxWorld || !pr.epoch) return PIE_EUNSUPPORTED;
+    if (tp->mode == 1)   // producer tiles are pushed as whole 16-row, 32-byte pieces
+      for (int i = 0; i < nseg; ++i)
+        if (segs[i].N % 16 != 0) return PIE_EUNSUPPORTED;
+    if (tp->mode == 2 && q2_kpad(K) / 16 > 2 * kQ2Warps * 32) return PIE_EUNSUPPORTED;  // the one-barrier staging form
+    if (tp->mode == 2) a.f16 = 1;
+    a.tp_mode = tp->mode; a.tp_rank = pr.rank; a.tp_world = pr.world; a.tp_max_elems = pr.max_elems;
+    for (int i = 0; i < pr.world; ++i) a.tp_peer[i] = (uint8_t*)pr.base[i];
+    a.tp_epoch = (unsigned int*)pr.epoch;
+    a.tp_h_out = (uint16_t*)tp->h_out;
+    if (a.f16) a.lift_magic = 0x64006400u;
+  }
   a.lift_mask = 0x000f000fu; a.lift_mask2 = 0x00f000f0u; a.lift_magic = a.f16 ? 0x64006400u : 0x43004300u;
   return PIE_OK;
 }

@@ -30,12 +30,20 @@ struct Qmv2Args {
   int out_ld;
   const uint16_t* residual;
   int epi;
+  // fused tensor-parallel exchange (one row): 0 none; 1 producer -- the finished rows go into slot `tp_rank` of every
+  // peer's buffer instead of `out`; 2 consumer -- x = x (the residual stream) + bf16(sum over ranks of the slots),
+  // CTA 0 stores it to tp_h_out, then the usual norm / staging.  See pie_comm.cu for the buffer and the epoch protocol.
+  int tp_mode, tp_rank, tp_world, tp_max_elems;
+  uint8_t* tp_peer[8];
+  unsigned int* tp_epoch;   // local: [0] exchange number, [1] consumer departures, [2] producer departures
+  uint16_t* tp_h_out;
 };
 
 size_t qmv2_smem_bytes(int M, int K);
 bool qmv2_supported(int M, int K, int bits, int group_size, const pie_qmv_seg* segs, int nseg, int dual);
 int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs,
-                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual);
+                    int nseg, const void* norm_weight, float eps, int epilogue, const void* residual,
+                    const pie_tp_fused* tp = nullptr);
 cudaError_t launch_qmv2(const Qmv2Args& a, bool pdl, cudaStream_t st);
 
 

@@ -365,6 +365,19 @@ __device__ __forceinline__ void q2_stage_x1(const Qmv2Args& a, uint8_t* var, flo
   const bool norm = a.norm_w != nullptr;
   uint4 xb[MAXU][2], wb[MAXU][2];
   float ss = 0.f, amax = 0.f;
+  // Consumer side of a fused tensor-parallel exchange: every rank's o / down projection pushed its partial row into
+  // slot r of this rank's buffer (pie_comm.cu has the layout); wait for the `world` flags of this exchange, then
+  // x = residual + bf16(sum of the slots in rank order) -- the all_sum + `h + r` of the reference, in the x load.
+  const bool tp = a.tp_mode == 2;
+  unsigned int tp_set = 0;
+  if (tp) {
+    const unsigned int e = *reinterpret_cast<volatile unsigned int*>(a.tp_epoch);
+    tp_set = e & 1u;
+    if (tid < a.tp_world)
+      wait_flag(reinterpret_cast<unsigned int*>(a.tp_peer[a.tp_rank] + tp_flags_off(a.tp_world, a.tp_max_elems)) +
+                    ((size_t)tp_set * a.tp_world + tid) * kTpMaxCtas, e);
+    __syncthreads();
+  }
 #pragma unroll
   for (int u = 0; u < MAXU; ++u) {
     const int b = u * NT + tid;
@@ -375,6 +388,30 @@ __device__ __forceinline__ void q2_stage_x1(const Qmv2Args& a, uint8_t* var, flo
       if (norm) {
         const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + b * 16);
         wb[u][0] = __ldg(wp); wb[u][1] = __ldg(wp + 1);
+      }
+      if (tp) {
+        float acc[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+        const uint16_t* mine = reinterpret_cast<const uint16_t*>(a.tp_peer[a.tp_rank]) +
+                               (size_t)tp_set * a.tp_world * a.tp_max_elems + b * 16;
+        for (int r = 0; r < a.tp_world; ++r) {
+          const uint4 p0 = ldcg128(mine + (size_t)r * a.tp_max_elems), p1 = ldcg128(mine + (size_t)r * a.tp_max_elems + 8);
+          const uint32_t pw[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { acc[2 * j] += bf16lo(pw[j]); acc[2 * j + 1] += bf16hi(pw[j]); }
+        }
+        const uint32_t hw[8] = {xb[u][0].x, xb[u][0].y, xb[u][0].z, xb[u][0].w, xb[u][1].x, xb[u][1].y, xb[u][1].z, xb[u][1].w};
+        uint32_t o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          o[j] = pack_bf16(bf16lo(hw[j]) + bfround(acc[2 * j]), bf16hi(hw[j]) + bfround(acc[2 * j + 1]));
+        xb[u][0] = make_uint4(o[0], o[1], o[2], o[3]);
+        xb[u][1] = make_uint4(o[4], o[5], o[6], o[7]);
+        if (blockIdx.x == 0 && a.tp_h_out) {   // the new residual stream, for the next exchange's consumer
+          uint4* dst = reinterpret_cast<uint4*>(a.tp_h_out + b * 16);
+          dst[0] = xb[u][0]; dst[1] = xb[u][1];
+        }
       }
     }
   }

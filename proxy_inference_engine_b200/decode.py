@@ -72,12 +72,26 @@ class DecodeEngine:
             # exchange steps: one-shot pushes over NVLink peer memory (tp.TPExchange, csrc/pie_comm.cu) unless
             # PIE_TP_ONESHOT=0 or symmetric memory cannot be set up (then NCCL collectives, as in round 1)
             self.xch = None
+            self.xch_f = None
             self.part = torch.empty((B, h), dtype=bf, device=dev)
             if os.environ.get("PIE_TP_ONESHOT", "1") != "0" and B * h <= 131072:
                 try:
                     from .tp import TPExchange
                     self.xch = TPExchange(self.tp, B * h, B, a.vocab_size // w, dev)
                     self.logits = self.xch.gathered   # peers write their vocabulary slices straight into it
+                    # PIE_TP_FUSED=1 (batch 1, 4-bit): the all-reduce FUSED into the GEMVs around it (pie_qmv_fused_tp):
+                    # the o / down projection pushes its partial row to every peer, the next matrix's x load adds the
+                    # slots and the residual.  Its own buffer and exchange numbers; the residual stream alternates
+                    # between h and h2.  Parity-green but measured SLOWER than the stand-alone exchange kernel on 2 x B200
+                    # (8B bs1: 502 vs 572 tok/s): every producer CTA pays a system-scope fence before it may signal, and
+                    # that sits on the critical path of the next matrix -- hence opt-in.
+                    self.xch_f = None
+                    if B == 1 and self.bits == 4 and os.environ.get("PIE_TP_FUSED", "0") == "1":
+                        self.xch_f = TPExchange(self.tp, h, 1, 8, dev)
+                        self.h2 = torch.empty_like(self.h)
+                        self.tpf_push = self.xch_f.fused(1)
+                        self.tpf_to_h2 = self.xch_f.fused(2, self.h2)
+                        self.tpf_to_h = self.xch_f.fused(2, self.h)
                 except Exception as e:  # pragma: no cover - depends on the box
                     import warnings
                     warnings.warn(f"one-shot tensor-parallel exchange unavailable ({e!r}); using NCCL collectives")
@@ -186,10 +200,11 @@ class DecodeEngine:
         self._plan_keep = (layers, sm, io)
 
     # ------------------------------------------------------------------------------------------------
-    def _qmv(self, out, out_ld, x, x_ld, K, segs, nseg, norm_w, epi, residual):
-        _lib.check(self.L.pie_qmv_fused(_p(out), out_ld, _p(x), x_ld, self.B, K, segs, nseg, self.gs, self.bits,
-                                        _p(norm_w), float(self.args.rms_norm_eps), epi, _p(residual), 0,
-                                        _p(self.qmv_ws), self.qmv_ws.numel(), self.pdl, _stream()), "qmv_fused")
+    def _qmv(self, out, out_ld, x, x_ld, K, segs, nseg, norm_w, epi, residual, tpf=None):
+        _lib.check(self.L.pie_qmv_fused_tp(_p(out), out_ld, _p(x), x_ld, self.B, K, segs, nseg, self.gs, self.bits,
+                                           _p(norm_w), float(self.args.rms_norm_eps), epi, _p(residual), 0,
+                                           _p(self.qmv_ws), self.qmv_ws.numel(), self.pdl,
+                                           C.byref(tpf) if tpf is not None else None, _stream()), "qmv_fused")
 
     def _qmv_rowsplit(self, h, hid, x, K, segs):
         """h += x @ W^T for a matrix split by input columns (o_proj, down_proj).  Single GPU: residual-add epilogue.
@@ -223,10 +238,15 @@ class DecodeEngine:
         qd = self.Hq * self.D
         import os
         skip = set(filter(None, os.environ.get("PIE_DEBUG_SKIP", "").split(",")))  # tools/bench_step_parts.py only
+        fz = self.tp_on and getattr(self, "xch_f", None) is not None   # all-reduces fused into the GEMVs (batch 1)
         for i, ly in enumerate(m.layers):
             if "qkv" not in skip:
-                self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
-                          EPI_STORE, None)
+                if fz and i > 0:   # x = h2 + (down partials of the previous layer); the new stream lands in h
+                    self._qmv(self.qkv, self.qkv.shape[1], self.h2, hid, hid, self.seg_qkv[i], 3,
+                              ly.input_layernorm.weight, EPI_STORE, None, self.tpf_to_h)
+                else:
+                    self._qmv(self.qkv, self.qkv.shape[1], h, hid, hid, self.seg_qkv[i], 3, ly.input_layernorm.weight,
+                              EPI_STORE, None)
             if "attn" not in skip and self.attn_fused:
                 _lib.check(L.pie_decode_attn_fused(_p(self.attn), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                                    C.byref(self.lay[i]), _p(self.positions),
@@ -242,6 +262,13 @@ class DecodeEngine:
                                          C.byref(self.lay[i]), _p(self.positions), self.B, self.Hq, self.Hkv, self.D,
                                          float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),
                                          self.attn_ws.numel(), _stream()), "decode_attn")
+            if fz:
+                self._qmv(self.part, hid, self.attn, qd, qd, self.seg_o[i], 1, None, EPI_STORE, None, self.tpf_push)
+                self._qmv(self.act, a.intermediate_size, h, hid, hid, self.seg_gu[i], 2,
+                          ly.post_attention_layernorm.weight, EPI_SILUMUL, None, self.tpf_to_h2)
+                self._qmv(self.part, hid, self.act, a.intermediate_size, a.intermediate_size, self.seg_down[i], 1, None,
+                          EPI_STORE, None, self.tpf_push)
+                continue
             if "o" not in skip:
                 self._qmv_rowsplit(h, hid, self.attn, qd, self.seg_o[i])
             if "gu" not in skip:
@@ -251,7 +278,11 @@ class DecodeEngine:
                 self._qmv_rowsplit(h, hid, self.act, a.intermediate_size, self.seg_down[i])
         if self.tp_on:
             nl = self.logits_local.shape[1]
-            self._qmv(self.logits_local, nl, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
+            if fz:   # x = h2 + (down partials of the last layer)
+                self._qmv(self.logits_local, nl, self.h2, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None,
+                          self.tpf_to_h)
+            else:
+                self._qmv(self.logits_local, nl, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
             if self.xch is not None:
                 self.xch.all_gather(self.logits_local, _stream())
                 _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),

@@ -121,7 +121,7 @@ class TPExchange:
         self.buf = symm.empty(int(nbytes), dtype=torch.uint8, device=device)
         self.buf.zero_()
         self.hdl = symm.rendezvous(self.buf, group)
-        self.epoch = torch.tensor([1, 0], dtype=torch.int32, device=device)
+        self.epoch = torch.tensor([1, 0, 0, 0], dtype=torch.int32, device=device)  # number, departures (2 kinds)
         self.peers = _lib.TpPeers()
         for r, ptr in enumerate(self.hdl.buffer_ptrs):
             self.peers.base[r] = ptr
@@ -132,6 +132,16 @@ class TPExchange:
         self._C = C
         torch.cuda.synchronize(device)
         dist.barrier(group=group)  # every rank's buffer is zeroed before anyone pushes into it
+
+    def fused(self, mode: int, h_out=None):
+        """pie_tp_fused descriptor for pie_qmv_fused_tp: mode 1 = producer (partial row pushed to every peer), mode 2 =
+        consumer (x = residual + sum of the slots, new residual stream stored to h_out).  Keep the object alive."""
+        from . import _lib
+        f = _lib.TpFused()
+        f.peers = self.peers
+        f.mode = mode
+        f.h_out = h_out.data_ptr() if h_out is not None else None
+        return f
 
     def all_reduce(self, out, partial, residual, stream):
         """out = bf16(residual + bf16(sum over ranks of partial)); partial [rows, width] bf16."""

@@ -125,5 +125,7 @@ def test_tensor_parallel_two_gpus_matches_single_gpu():
     """tools/tp_check.py under torchrun: the sharded engine against the single-GPU engine (tokens + logits)."""
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
            "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tools", "tp_check.py")]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
-    assert out.returncode == 0 and "TP_CHECK PASS" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+    for fused in ("0", "1"):   # the stand-alone one-shot exchange kernels, then the exchange fused into the GEMVs (bs1)
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=dict(os.environ, PIE_TP_FUSED=fused))
+        assert out.returncode == 0 and "TP_CHECK PASS" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+        assert ("_fused" in out.stdout) == (fused == "1")

@@ -17,7 +17,8 @@ out = {}
 GRAPH = os.environ.get("TP_GRAPH", "1") == "1"
 def mark(m):
     print(f"[rank {rank}] {m}", flush=True)
-for bits, tie in ((4, False), (8, True)):
+# batch 1 with 4-bit weights takes the FUSED exchange (all-reduce inside the GEMVs); the other cases the one-shot kernels
+for bits, tie, B in ((4, False, 1), (4, False, 2), (8, True, 2)):
     args = ModelArgs(hidden_size=1024, num_hidden_layers=3, intermediate_size=2048, num_attention_heads=8,
                      num_key_value_heads=world if world > 2 else 2, head_dim=128, vocab_size=1024, rms_norm_eps=1e-5,
                      rope_theta=500000.0, max_position_embeddings=131072, tie_word_embeddings=tie,
@@ -26,7 +27,7 @@ for bits, tie in ((4, False), (8, True)):
     full = random_weights(args, seed=0, device="cuda", gen_device="cpu")
     info = T.TPInfo(rank, world)
     model = build_model(T.shard_args(args, world), T.shard_weights(full, args, rank, world)).set_tp(info)
-    B, Lp, steps = 2, 24, 16
+    Lp, steps = 24, 16
     prompt = torch.randint(0, args.vocab_size, (B, Lp), generator=torch.Generator().manual_seed(1))
     mark("model built")
     eng = DecodeEngine(model, batch=B, max_context=Lp + steps + 8, use_graph=GRAPH)
@@ -49,7 +50,7 @@ for bits, tie in ((4, False), (8, True)):
         same = (toks == ref.generated()).all(0).cpu().numpy().tolist()
         n_same = same.index(False) if False in same else len(same)
         err = float((a[:max(n_same - 1, 1)] - b[:max(n_same - 1, 1)]).norm() / b[:max(n_same - 1, 1)].norm())
-        out[f"q{bits}{'_tied' if tie else ''}"] = {"rel_err": round(err, 5), "tokens_equal_steps": n_same, "steps": steps + 1}
+        out[f"q{bits}{'_tied' if tie else ''}_bs{B}" + ("_fused" if getattr(eng, "xch_f", None) is not None else "")] = {"rel_err": round(err, 5), "tokens_equal_steps": n_same, "steps": steps + 1}
     dist.barrier()
 if rank == 0:
     print(json.dumps({"world": world, "results": out}))
