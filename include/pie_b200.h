@@ -167,6 +167,18 @@ int pie_argmax(int32_t* out_idx, const void* logits, int rows, int vocab, int32_
                int32_t* seq_out, int seq_ld, void* stream);
 
 
+/* ---- (f1) the rest of the sampler, on the device: logprobs = f32(logits) - logsumexp (PIE/engine/inference_engine.py:
+ * 268-269) and make_sampler's temperature branches (PIE/samplers/__init__.py:11-45: top_p.py, min_p.py, top_k.py,
+ * categorical.py; precedence top_p, then min_p, then top_k, else plain categorical), one launch per step.
+ * temp must be > 0 (temp == 0 is pie_argmax).  The categorical draw is the arg-max of logprobs / temp + Gumbel noise over
+ * the kept tokens.  Noise: Philox4x32-10 keyed by rng_state (DEVICE memory, 32 bytes: u64 seed, u64 draw counter, 16
+ * bytes of scratch -- zero at start; the kernel advances the counter, so a captured graph draws fresh numbers on every
+ * replay), or `uniforms` (f32 [rows, vocab] in (0, 1)) when given.  logprobs_out (optional) f32 [rows, vocab].
+ * positions_to_advance / seq_out as for pie_argmax.  logits bf16 [rows, ld >= vocab]. */
+int pie_sample(int32_t* tokens, const void* logits, int rows, int vocab, int ld, float temp, float top_p, float min_p,
+               int min_tokens_to_keep, int top_k, void* rng_state, const float* uniforms, float* logprobs_out,
+               int32_t* positions_to_advance, int32_t* seq_out, int seq_ld, void* stream);
+
 /* ---- (e) tensor-parallel exchange steps, one-shot over NVLink peer memory ----------------------------------------
  * Replace the collectives of MLX's sharded linears at decode sizes: `all_sum` after a row-split matrix
  * (QuantizedShardedToAllLinear, MLX/python/mlx/nn/layers/distributed.py:459-566) and the gather of vocabulary-split

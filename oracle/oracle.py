@@ -319,6 +319,54 @@ def add(a, b, mode: str = "B") -> np.ndarray:
 # --------------------------------------------------------------------------------------------
 # model: the wiring of PIE/models/llama/language.py
 # --------------------------------------------------------------------------------------------
+# --------------------------------------------------------------------------------------------
+# sampler (PIE/engine/inference_engine.py:268-271; PIE/samplers/*.py) -- numpy restatement
+# --------------------------------------------------------------------------------------------
+def logprobs_of(logits) -> np.ndarray:
+    """logits_f32 - logsumexp(logits_f32, axis=-1, keepdims=True)   (inference_engine.py:268-269)"""
+    x = np.asarray(logits, dtype=np.float32)
+    m = x.max(axis=-1, keepdims=True)
+    return x - (m + np.log(np.exp(x - m).sum(axis=-1, keepdims=True, dtype=np.float32)))
+
+
+def _categorical(x, uniforms) -> np.ndarray:
+    """mx.random.categorical = arg-max of logits + Gumbel noise; the noise is given as uniforms in (0, 1)."""
+    g = -np.log(-np.log(np.asarray(uniforms, dtype=np.float32)))
+    return np.argmax(np.where(np.isneginf(x), -np.inf, x + g), axis=-1).astype(np.int32)
+
+
+def sample_reference(logprobs, uniforms, temp, top_p=0.0, min_p=0.0, min_tokens_to_keep=1, top_k=-1) -> np.ndarray:
+    """make_sampler (PIE/samplers/__init__.py:11-45) for temp > 0, statement for statement, with the random draw taken
+    from `uniforms` [rows, vocab] (uniforms[r, i] belongs to TOKEN i, whatever order a sampler sorts the tokens in)."""
+    lp = np.asarray(logprobs, dtype=np.float32)
+    u = np.asarray(uniforms, dtype=np.float32)
+    if 0 < top_p < 1.0:                                   # top_p.py:8-37
+        x = lp * np.float32(1 / temp)
+        p = np.exp(x - x.max(-1, keepdims=True)); p = (p / p.sum(-1, keepdims=True, dtype=np.float32)).astype(np.float32)
+        idx = np.argsort(p, axis=-1, kind="stable")
+        sp = np.take_along_axis(p, idx, -1)
+        cum = np.cumsum(sp, axis=-1, dtype=np.float32)
+        top = np.where(cum > 1 - top_p, sp, 0)
+        with np.errstate(divide="ignore"):
+            tok = _categorical(np.log(top), np.take_along_axis(u, idx, -1))
+        return np.take_along_axis(idx, tok[:, None].astype(np.int64), -1)[:, 0].astype(np.int32)
+    if min_p != 0.0:                                      # min_p.py:8-67
+        x = lp * np.float32(1 / temp)
+        idx = np.argsort(-x, axis=-1, kind="stable")
+        sx = np.take_along_axis(x, idx, -1)
+        remove = sx < sx[:, 0:1] + np.float32(np.log(min_p))
+        remove[..., :min_tokens_to_keep] = False
+        tok = _categorical(np.where(remove, -np.inf, sx), np.take_along_axis(u, idx, -1))
+        return np.take_along_axis(idx, tok[:, None].astype(np.int64), -1)[:, 0].astype(np.int32)
+    if top_k > 0:                                         # top_k.py:8-35
+        x = lp * np.float32(1 / temp)
+        mask_idx = np.argpartition(-x, kth=top_k - 1, axis=-1)[..., top_k:]
+        masked = x.copy()
+        np.put_along_axis(masked, mask_idx, -np.inf, axis=-1)
+        return _categorical(masked, u)
+    return _categorical(lp * np.float32(1 / temp), u)     # categorical.py:6-8
+
+
 @dataclass
 class ModelArgs:
     """PIE/models/llama/language.py:13-29."""

@@ -97,6 +97,7 @@ SIGNATURES = {
     "pie_tp_gather_offset": (_sz, [_i, _i]),
     "pie_tp_allreduce": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(TpPeers), _vp]),
     "pie_tp_allgather": (_i, [_vp, _i, _i, C.POINTER(TpPeers), _vp]),
+    "pie_sample": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _f, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "pie_decode_step_plan_bytes": (_sz, [_i]),
     "pie_decode_step_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_step_attn_ws_bytes": (_sz, [_i, _i, _i, _i]),

@@ -40,8 +40,20 @@ def _segs(*linears):
 class DecodeEngine:
     def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
                  use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2,
-                 fused: bool = False, trace: bool = False, attn_fused: bool | None = None, tp=None):
+                 fused: bool = False, trace: bool = False, attn_fused: bool | None = None, tp=None,
+                 sampling: dict | None = None):
+        """sampling: make_sampler's arguments (temp, top_p, min_p, min_tokens_to_keep, top_k; PIE/samplers/__init__.py:11)
+        plus `seed`; None or temp == 0 is greedy.  With temp > 0 every step ends in pie_sample instead of pie_argmax, inside
+        the captured graph (the Philox draw counter lives in device memory), and token ids still never leave the GPU."""
         a = model.args
+        sp = dict(sampling or {})
+        self.sampling = None
+        if sp.get("temp", 0.0) > 0:
+            if fused:
+                raise ValueError("the one-launch decode step samples greedily; use the per-operator path with sampling")
+            self.sampling = dict(temp=float(sp["temp"]), top_p=float(sp.get("top_p", 0.0)), min_p=float(sp.get("min_p", 0.0)),
+                                 min_tokens_to_keep=int(sp.get("min_tokens_to_keep", 1)), top_k=int(sp.get("top_k", -1)))
+            self.rng_state = ops.new_rng_state(sp.get("seed", 0), model.model.norm.weight.device)
         self.model, self.args, self.B, self.max_context = model, a, batch, max_context
         self.pdl, self.use_graph = int(pdl), use_graph
         dev = model.model.norm.weight.device
@@ -285,16 +297,23 @@ class DecodeEngine:
                 self._qmv(self.logits_local, nl, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
             if self.xch is not None:
                 self.xch.all_gather(self.logits_local, _stream())
-                _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
-                                        _p(self.seq), self.seq.shape[1], _stream()), "argmax")
+                self._sample()
                 return
             dist.all_gather_into_tensor(self.logits_gather, self.logits_local, group=self.tp.group)
             self.logits.view(self.B, self.tp.world, nl).copy_(
                 self.logits_gather.view(self.tp.world, self.B, nl).permute(1, 0, 2))
         else:
             self._qmv(self.logits, a.vocab_size, h, hid, hid, self.seg_head, 1, m.model.norm.weight, EPI_STORE, None)
-        _lib.check(L.pie_argmax(_p(self.tokens), _p(self.logits), self.B, a.vocab_size, _p(self.positions),
-                                _p(self.seq), self.seq.shape[1], _stream()), "argmax")
+        self._sample()
+
+    def _sample(self, logits=None):
+        """tokens = sampler(logits); positions += 1; seq[b, pos] = token   (inference_engine.py:268-271), one launch."""
+        lg = self.logits if logits is None else logits
+        if self.sampling is None:
+            ops.argmax(lg, positions_to_advance=self.positions, seq_out=self.seq, out=self.tokens)
+        else:
+            ops.sample(lg, rng_state=self.rng_state, positions_to_advance=self.positions, seq_out=self.seq,
+                       out=self.tokens, **self.sampling)
 
     def enqueue_gemvs(self):
         """Only the quantized matmuls of one step (4 per layer + head), same descriptors, no collectives: bench.py times
@@ -376,8 +395,7 @@ class DecodeEngine:
         self.prompt_len = Lp
         last = logits[:, -1, :].contiguous()
         self.logits.copy_(last)
-        ops_tok = ops.argmax(last, positions_to_advance=self.positions, seq_out=self.seq)
-        self.tokens.copy_(ops_tok)
+        self._sample(self.logits)
         return self.tokens
 
     def step(self, n: int = 1):

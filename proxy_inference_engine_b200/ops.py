@@ -297,14 +297,54 @@ def add(a, b):
     return out
 
 
-def argmax(logits, positions_to_advance=None, seq_out=None):
+def argmax(logits, positions_to_advance=None, seq_out=None, out=None):
     """Greedy sampler (temp == 0): first arg-max of each row of bf16 logits [rows, vocab] -> int32 [rows]."""
     logits = logits.contiguous()
     rows, vocab = logits.shape
-    out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
+    if out is None:
+        out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
     _lib.check(_lib.load().pie_argmax(_p(out), _p(logits), rows, vocab, _p(positions_to_advance), _p(seq_out),
                                       0 if seq_out is None else seq_out.shape[1], _stream()), "argmax")
     return out
+
+
+def new_rng_state(seed: int, device="cuda") -> torch.Tensor:
+    """Device-resident Philox state of pie_sample: [seed, draw counter, scratch, scratch] (int64)."""
+    return torch.tensor([int(seed) & 0x7FFFFFFFFFFFFFFF, 0, 0, 0], dtype=torch.int64, device=device)
+
+
+def sample(logits, temp: float, top_p: float = 0.0, min_p: float = 0.0, min_tokens_to_keep: int = 1, top_k: int = -1,
+           rng_state=None, uniforms=None, return_logprobs: bool = False, positions_to_advance=None, seq_out=None,
+           out=None, logprobs_out=None):
+    """The temperature branches of make_sampler (PIE/samplers/__init__.py:11-45) on bf16 logits [rows, vocab], in one
+    launch together with logprobs = f32(logits) - logsumexp (inference_engine.py:268-269).  Returns tokens (int32 [rows])
+    or (tokens, logprobs f32 [rows, vocab])."""
+    if temp <= 0:
+        raise ValueError("[sample] temp must be > 0 (temp == 0 is argmax)")
+    if not (0 <= min_p <= 1.0):
+        raise ValueError(f"`min_p` has to be a float in the [0, 1] interval, but is {min_p}")          # min_p.py:33-36
+    if not isinstance(min_tokens_to_keep, int) or min_tokens_to_keep < 1:
+        raise ValueError(f"`min_tokens_to_keep` has to be a positive integer, but is {min_tokens_to_keep}")  # :37-40
+    logits = logits.contiguous()
+    rows, vocab = logits.shape
+    use_top_k = not (0 < top_p < 1.0) and min_p == 0.0 and top_k > 0
+    if use_top_k and not (isinstance(top_k, int) and 0 < top_k < vocab):
+        raise ValueError(f"`top_k` has to be an integer in the (0, {vocab}] interval, but is {top_k}.")  # top_k.py:23-27
+    if logits.dtype != _BF16:
+        raise ValueError("[sample] only bfloat16 logits are built here")
+    if rng_state is None and uniforms is None:
+        raise ValueError("[sample] needs rng_state (ops.new_rng_state) or uniforms")
+    if out is None:
+        out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
+    if return_logprobs and logprobs_out is None:
+        logprobs_out = torch.empty((rows, vocab), dtype=torch.float32, device=logits.device)
+    if uniforms is not None:
+        uniforms = uniforms.to(torch.float32).contiguous()
+    _lib.check(_lib.load().pie_sample(_p(out), _p(logits), rows, vocab, vocab, float(temp), float(top_p), float(min_p),
+                                      int(min_tokens_to_keep), int(top_k), _p(rng_state), _p(uniforms), _p(logprobs_out),
+                                      _p(positions_to_advance), _p(seq_out), 0 if seq_out is None else seq_out.shape[1],
+                                      _stream()), "sample")
+    return (out, logprobs_out) if return_logprobs else out
 
 
 def launch_count() -> int:
