@@ -143,10 +143,17 @@ int pie_decode_attn(void* out, const void* q, const void* kcache, const void* vc
  * (Attention.__call__ PIE/models/llama/language.py:84-104 for L == 1).  qkv bf16 [B, (Hq + 2 Hkv) D] un-rotated, as
  * the fused q/k/v projection writes it; out bf16 [B, Hq D].  One CTA of 16 warps per (row, kv head, pair of query
  * heads, context split); the appended token is read from qkv, older ones from the cache.  Workspace and nsplit as
- * for pie_decode_attn (pie_decode_step_pick_splits sizes nsplit for this kernel).                              */
+ * for pie_decode_attn (pie_decode_step_pick_splits sizes nsplit for this kernel).
+ * rope_table (optional, pie_rope_table): sin / cos of the angles of positions[], computed once per step for all
+ * layers; NULL = every launch computes them from freqs.  Position-only work (angles, the cache rows of older tokens)
+ * runs before the launch's dependency wait: positions[] and the cache rows below positions[b] must not be written by
+ * the kernel launched just before this one.                                                                        */
+int pie_rope_table(float* table /* f32 [B][2][half_dims] */, const int32_t* positions, const float* freqs, int B,
+                   int half_dims, void* stream);
 int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache, const pie_kv_layout* kv_host,
-                          const int32_t* positions, const float* freqs, int B, int Hq, int Hkv, int D, float scale,
-                          int nsplit, void* workspace, size_t workspace_bytes, int pdl, void* stream);
+                          const int32_t* positions, const float* freqs, const float* rope_table, int B, int Hq,
+                          int Hkv, int D, float scale, int nsplit, void* workspace, size_t workspace_bytes, int pdl,
+                          void* stream);
 
 /* ---- a10 SDPA for L > 1 with the additive causal mask of create_attention_mask (PIE/models/base.py:18-53)
  * q bf16 [B, Hq, L, D]; k,v read from the cache (T = offset + L tokens); out bf16 [B, L, Hq * D].       */
@@ -266,6 +273,13 @@ size_t pie_decode_step_attn_ws_bytes(int B, int Hq, int D, int nsplit);
 int pie_decode_step_plan(const pie_step_model* model, const pie_step_layer* layers, const pie_step_io* io,
                          void* plan_host, size_t plan_bytes);
 int pie_decode_step(const void* plan_dev, const void* plan_host, size_t plan_bytes, void* sync_ws, void* stream);
+
+/* Profiling aid (no reference counterpart): after this call every TMA GEMV and fused-attention launch writes up to
+ * sixteen %globaltimer stamps per CTA (entry, first loads issued, dependency wait returned, activations staged, first
+ * weights landed, main loop done, CTA reduction, exit, ...) into the next 32 KB slot of `buf` (device memory).  NULL
+ * switches it off.  A launch takes its slot when it is ENQUEUED, so a captured CUDA graph keeps writing the slots it was
+ * captured with.  tools/timeline_step.py prints the timeline of a decode step from it. */
+int pie_debug_stamps(void* buf, size_t bytes);
 
 #ifdef __cplusplus
 }

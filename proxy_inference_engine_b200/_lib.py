@@ -85,8 +85,9 @@ SIGNATURES = {
     "pie_decode_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "pie_decode_attn_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
-    "pie_decode_attn_fused": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _vp, _i, _i, _i, _i, _f, _i, _vp, _sz,
-                                   _i, _vp]),
+    "pie_rope_table": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "pie_decode_attn_fused": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _vp,
+                                   _sz, _i, _vp]),
     "pie_prefill_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _i, _i, _i, _i, _i, _i, _f, _vp]),
     "pie_silu_mul": (_i, [_vp, _vp, _vp, _ll, _vp]),
     "pie_add": (_i, [_vp, _vp, _vp, _ll, _vp]),
@@ -97,6 +98,7 @@ SIGNATURES = {
     "pie_tp_gather_offset": (_sz, [_i, _i]),
     "pie_tp_allreduce": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(TpPeers), _vp]),
     "pie_tp_allgather": (_i, [_vp, _i, _i, C.POINTER(TpPeers), _vp]),
+    "pie_debug_stamps": (_i, [_vp, _sz]),
     "pie_sample": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _f, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "pie_decode_step_plan_bytes": (_sz, [_i]),
     "pie_decode_step_pick_splits": (_i, [_i, _i, _i, _i]),

@@ -104,6 +104,41 @@ def build_model(args: ModelArgs, weights: dict, device="cuda") -> Model:
     return model
 
 
+def colocate_for_decode(model: Model) -> None:
+    """Re-home the quantized matrices of the decode GEMVs so that one TMA copy brings what used to take several
+    (csrc/pie_qmv2.h, Qmv2Args): every matrix's biases directly behind its scales, and each layer's up projection directly
+    behind its gate projection.  Every array keeps the MLX layout (the modules hold views into the new storage);
+    idempotent; costs one extra copy of a layer at a time while it runs."""
+    def stacked(a, b):
+        return b.data_ptr() - a.data_ptr() == a.numel() * a.element_size() and a._base is not None and a._base is b._base
+
+    def scales_biases(lin):
+        if stacked(lin.scales, lin.biases):
+            return
+        st = torch.empty((2,) + tuple(lin.scales.shape), dtype=lin.scales.dtype, device=lin.scales.device)
+        st[0].copy_(lin.scales); st[1].copy_(lin.biases)
+        lin.scales, lin.biases = st[0], st[1]
+
+    for ly in model.layers:
+        at, mlp = ly.self_attn, ly.mlp
+        for lin in (at.q_proj, at.k_proj, at.v_proj, at.o_proj, mlp.down_proj):
+            scales_biases(lin)
+        g, u = mlp.gate_proj, mlp.up_proj
+        if g.weight.shape != u.weight.shape:
+            scales_biases(g); scales_biases(u)
+            continue
+        if not stacked(g.weight, u.weight):
+            w = torch.empty((2,) + tuple(g.weight.shape), dtype=g.weight.dtype, device=g.weight.device)
+            w[0].copy_(g.weight); w[1].copy_(u.weight)
+            g.weight, u.weight = w[0], w[1]
+        if not (stacked(g.scales, u.scales) and stacked(g.biases, u.biases)):
+            sb = torch.empty((2, 2) + tuple(g.scales.shape), dtype=g.scales.dtype, device=g.scales.device)   # [s|b][gate|up]
+            sb[0, 0].copy_(g.scales); sb[0, 1].copy_(u.scales); sb[1, 0].copy_(g.biases); sb[1, 1].copy_(u.biases)
+            g.scales, u.scales, g.biases, u.biases = sb[0, 0], sb[0, 1], sb[1, 0], sb[1, 1]
+    head = model.model.embed_tokens if model.args.tie_word_embeddings else model.lm_head
+    scales_biases(head)
+
+
 def _as_param(v: torch.Tensor, device):
     v = v.to(device)
     return v.view(torch.int32) if v.dtype == torch.uint32 else v

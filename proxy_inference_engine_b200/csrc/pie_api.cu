@@ -292,5 +292,12 @@ int pie_qmv(void* y, const void* x, const uint32_t* wq, const void* scales, cons
                                         (const uint16_t*)biases, M, N, K, group_size, bits, (cudaStream_t)stream));
 }
 
+// profiling aid: from now on every TMA GEMV / fused-attention launch writes %globaltimer stamps of its CTAs into the next
+// 32 KB slot of `buf` (device memory, zeroed by the caller); nullptr switches it off.  See tools/timeline_step.py.
+int pie_debug_stamps(void* buf, size_t bytes) {
+  debug_stamps(buf, bytes);
+  return PIE_OK;
+}
+
 }  // extern "C"
 #include "pie_api2.inl"

@@ -192,6 +192,18 @@ __device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t 
   return d;
 }
 
+// sin / cos of a rotary angle theta >= 0 (up to ~1e5 rad): theta is reduced to [-pi, pi] with 2 pi split in two fp32 pieces
+// (each FMA rounds once, at magnitude <= pi: ~2.5e-7 absolute), then the SFU approximations (~5e-7 absolute on that range).
+// The rotated values are rounded to bf16 (2^-9 relative); the library sincosf costs ~500 cycles per call here because of
+// its large-argument path.  Every rotary kernel of this library uses this one function, so they agree bit for bit.
+__device__ __forceinline__ void rope_sincos(float theta, float* sn, float* cs) {
+  const float k = rintf(theta * 0.15915494309189535f);
+  float r = fmaf(-k, 6.2831854820251465f, theta);
+  r = fmaf(k, 1.7484555e-7f, r);
+  *sn = __sinf(r);
+  *cs = __cosf(r);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -56,14 +56,23 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: TMA operands stay in uniform registers
   const int g = lane >> 2, t = lane & 3;
   constexpr int COLS = ONECOL ? 1 : 8;
+#define Q2_STAMP(i)                                                                        \
+  if (a.stamps && tid == 0) {                                                              \
+    unsigned long long t_;                                                                 \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                 \
+    a.stamps[blockIdx.x * 16 + (i)] = t_;                                                  \
+  }
+  Q2_STAMP(0)
 
   // ---- this CTA's tiles and this warp's run of units -------------------------------------------------
-  const int G = gridDim.x, c = blockIdx.x;
-  const int tile_lo = (int)((long long)c * a.ntiles / G), tile_hi = (int)((long long)(c + 1) * a.ntiles / G);
+  // (no divisions here: this prologue is on the launch's critical path)
+  const int c = blockIdx.x;
+  const int tile_lo = c * a.tiles_q + min(c, a.tiles_r), tile_hi = tile_lo + a.tiles_q + (c < a.tiles_r ? 1 : 0);
   const int upt = a.upt;
   const int cu = (tile_hi - tile_lo) * upt;                 // units of this CTA
-  const int ub = tile_lo * upt + (int)((long long)warp * cu / kQ2Warps);
-  const int ue = tile_lo * upt + (int)((long long)(warp + 1) * cu / kQ2Warps);
+  const int ub = tile_lo * upt + ((warp * cu) >> 4);
+  const int ue = tile_lo * upt + (((warp + 1) * cu) >> 4);
+  static_assert(kQ2Warps == 16, "the warp split above shifts by 4");
 
   const uint32_t smem_s = smem_u32(smem);
   const uint32_t wst = smem_s + (uint32_t)(warp * kQ2Stages) * kQ2WBytes;
@@ -74,45 +83,25 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   uint8_t* var = smem + kQ2VarOff;
 
   const uint64_t pol = l2_policy_evict_first();
-  // (tile, k chunk) -> three (dual: six) TMA copies into stage st
+  // (tile, k chunk) -> the unit's TMA copies into stage st
   auto issue = [&](int tile, int kc, int st) {
-    const uint32_t bar = bar0 + st * 8, wd = wst + st * kQ2WBytes, sd = sbst + st * kQ2SbBytes;
-    if (a.dbg & 2) {  // experiment: weights only
-      mbar_expect_tx_s(bar, kQ2WBytes);
-      if (DUAL) {
-        tma_load_3d(wd, &a.wmap[0], bar, 0, tile * 8, 2 * kc, pol);
-        tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, tile * 8, 2 * kc, pol);
-      } else {
-        tma_load_3d(wd, &a.wmap[0], bar, 0, (tile - a.tile0[0]) * 16, 2 * kc, pol);
-      }
-      return;
-    }
-    mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
-    if (DUAL) {
-      const int r0 = tile * 8;
-      tma_load_3d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, pol);
-      tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, pol);
-      tma_load_2d_b(sd, &a.smap[0], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 128, &a.smap[1], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 256, &a.bmap[0], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 384, &a.bmap[1], bar, 8 * kc, r0, pol);
-    } else {
-      int si = 0;
-      if (a.nseg > 1 && tile >= a.tile0[1]) si = 1;
-      if (a.nseg > 2 && tile >= a.tile0[2]) si = 2;
-      const int r0 = (tile - a.tile0[si]) * 16;
-      tma_load_3d(wd, &a.wmap[si], bar, 0, r0, 2 * kc, pol);
-      tma_load_2d_b(sd, &a.smap[si], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 256, &a.bmap[si], bar, 8 * kc, r0, pol);
-    }
+    q2_issue_unit(a, a, tile, kc, wst + st * kQ2WBytes, sbst + st * kQ2SbBytes, bar0 + st * 8, pol);
   };
   // producer cursor (lane 0 only): the next unit to request
-  int p_u = ub, p_tile = ub / upt, p_kc = ub - p_tile * upt;
+  const int p_tile0 = upt == 1 ? ub : (int)__umulhi((unsigned)ub, a.upt_inv);
+  int p_u = ub, p_tile = p_tile0, p_kc = ub - p_tile * upt;
   auto advance = [&]() {
     ++p_u;
     if (++p_kc == upt) { p_kc = 0; ++p_tile; }
   };
 
+  // the TMA unit fetches a descriptor on first use (cold: every launch has its own parameter buffer): ask for all of
+  // them at once, from different lanes, before anything else
+  if (warp == 0 && lane < 9) {
+    const int i = lane / 3, kind = lane - 3 * i;
+    if (i < (DUAL ? (a.gu_stacked ? 1 : 2) : a.nseg) && !(kind == 2 && a.sb_stacked))
+      tma_prefetch_desc(kind == 0 ? &a.wmap[i] : kind == 1 ? &a.smap[i] : &a.bmap[i]);
+  }
   if (lane == 0) {
     mbar_init_s(bar0, 1);
     mbar_init_s(bar0 + 8, 1);
@@ -121,14 +110,29 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     edge_tile[warp * 2] = -1;
     edge_tile[warp * 2 + 1] = -1;
   }
-  if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
-  if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+  // First loads: stage 0 before the dependency wait, stage 1 right behind the loads of x (measured: with both stages in
+  // flight before the wait, the 148 x 16 x 9 KB of weight traffic delays the x loads every CTA is about to wait for).
+  Q2_STAMP(8)
+  if (!(a.dbg & 4)) {
+    if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
+    if ((a.dbg & 8) && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+  }
+  auto after_x_loads = [&]() {
+    if (!(a.dbg & (4 | 8)) && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+  };
+  Q2_STAMP(1)
   pdl_launch_dependents();
   pdl_wait();
+  Q2_STAMP(2)
   unsigned int tp_e = 0, tp_set = 0;
   if (ONECOL && a.tp_mode == 1) { tp_e = *reinterpret_cast<volatile unsigned int*>(a.tp_epoch); tp_set = tp_e & 1u; }
-  q2_stage_x<ONECOL, F16>(a, var, red);
+  q2_stage_x<ONECOL, F16>(a, var, red, after_x_loads, a.stamps && tid == 0 ? a.stamps + blockIdx.x * 16 : nullptr);
   __syncthreads();
+  Q2_STAMP(3)
+  if (a.dbg & 4) {  // experiment: first loads only after the activations are staged
+    if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
+    if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+  }
 
   // ---- per-lane constants -------------------------------------------------------------------------
   const int kpad = q2_kpad(a.K), Gp = kpad / kGroup, gp = q2_gpitch(a.K);
@@ -222,7 +226,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
 
   // ---- main loop ---------------------------------------------------------------------------------------
   int run_start_kc = 0;  // k chunk at which this warp's share of the current tile began
-  int tile = ub / upt, kc = ub - tile * upt;
+  int tile = p_tile0, kc = ub - tile * upt;
   for (int u = ub; u < ue; ++u) {
     const int i = u - ub, st = i & 1;
     if (i == 0 || kc == 0) {
@@ -232,6 +236,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     }
     const bool tile_ends = kc == upt - 1 || u == ue - 1;
     const uint32_t tok = mbar_wait_s(bar0 + st * 8, (i >> 1) & 1);
+    if (i == 0) { Q2_STAMP(4) }
     const uint32_t wb = wst + st * kQ2WBytes, sb = sbst + st * kQ2SbBytes;
     if (!(a.dbg & 1)) {
       const uint32_t sp = sb + tok;
@@ -320,6 +325,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
       if (lane == 0) edge_tile[warp * 2 + 1] = tile_done;
     }
   }
+  Q2_STAMP(5)
   // park the first edge in this warp's stage 0 (every stage of this warp has been consumed by now)
   if (e0_tile >= 0) {
     asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(wst + lane * 16), "f"(e0v[0]), "f"(e0v[1]), "f"(e0v[2]),
@@ -331,6 +337,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   if (e0_tile >= 0 && (e0_tile + 1) * upt <= ue) fin_tile = e0_tile;   // edge 0 ends inside this run
   if (fin_tile >= 0 && a.epi == EPI_RESADD) load_residual(fin_tile);
   __syncthreads();
+  Q2_STAMP(6)
   if (fin_tile >= 0) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     for (int w2 = 0; w2 <= warp; ++w2) {
@@ -344,6 +351,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     }
     epilogue(fin_tile, v);
   }
+  Q2_STAMP(7)
   if (ONECOL && a.tp_mode == 1) {
     // producer: when this rank's LAST CTA is done, every peer may read slot `tp_rank` of exchange tp_e
     // (one fence by one thread behind the CTA barrier -- cumulative over the CTA's pushes -- not one per thread)
@@ -387,21 +395,27 @@ static EncodeTiledFn encode_fn() {
 }
 
 struct MapKey {
-  const void* ptr; int N, K, rows, kind;
-  bool operator==(const MapKey& o) const { return ptr == o.ptr && N == o.N && K == o.K && rows == o.rows && kind == o.kind; }
+  const void* ptr; int N, K, rows, kind, T, S; long long tstride, sstride;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && N == o.N && K == o.K && rows == o.rows && kind == o.kind && T == o.T && S == o.S &&
+           tstride == o.tstride && sstride == o.sstride;
+  }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.ptr);
-    h ^= (size_t)k.N * 0x9E3779B97F4A7C15ull + (size_t)k.K * 0xC2B2AE3D27D4EB4Full + (size_t)k.rows * 131 + k.kind;
+    h ^= (size_t)k.N * 0x9E3779B97F4A7C15ull + (size_t)k.K * 0xC2B2AE3D27D4EB4Full + (size_t)k.rows * 131 + k.kind +
+         (size_t)k.T * 7 + (size_t)k.S * 13 + (size_t)k.tstride * 31 + (size_t)k.sstride * 17;
     return h;
   }
 };
-// kind 0: packed 4-bit weights [N, K/2 bytes] as (128 B, rows, K/256 chunks); kind 1: bf16 scales / biases [N, K/64]
-static bool get_map(CUtensorMap* out, const void* ptr, int N, int K, int rows, int kind) {
+// kind 0: packed 4-bit weights [N, K/2 bytes] as (128 B, row, 256-k chunk, matrix t < T at byte stride tstride);
+// kind 1: bf16 scales / biases [N, K/64] as (group, row, matrix t < T, array s < S at byte stride sstride)
+static bool get_map(CUtensorMap* out, const void* ptr, int N, int K, int rows, int kind, int T, long long tstride, int S,
+                    long long sstride) {
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   static std::mutex mu;
-  const MapKey key{ptr, N, K, rows, kind};
+  const MapKey key{ptr, N, K, rows, kind, T, S, tstride, sstride};
   std::lock_guard<std::mutex> lk(mu);
   auto it = cache.find(key);
   if (it != cache.end()) { *out = it->second; return true; }
@@ -409,20 +423,20 @@ static bool get_map(CUtensorMap* out, const void* ptr, int N, int K, int rows, i
   if (!enc) return false;
   CUtensorMap m;
   CUresult r;
+  const cuuint32_t es[4] = {1, 1, 1, 1};
   if (kind == 0) {
-    const cuuint64_t dims[3] = {128, (cuuint64_t)N, (cuuint64_t)(K / 256)};
-    const cuuint64_t strides[2] = {(cuuint64_t)(K / 2), 128};
-    const cuuint32_t box[3] = {128, (cuuint32_t)rows, 2};
-    const cuuint32_t es[3] = {1, 1, 1};
-    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(ptr), dims, strides, box, es,
+    const cuuint64_t dims[4] = {128, (cuuint64_t)N, (cuuint64_t)(K / 256), (cuuint64_t)T};
+    const cuuint64_t strides[3] = {(cuuint64_t)(K / 2), 128, (cuuint64_t)(T > 1 ? tstride : 16)};
+    const cuuint32_t box[4] = {128, (cuuint32_t)rows, 2, (cuuint32_t)T};
+    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(ptr), dims, strides, box, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   } else {
-    const cuuint64_t dims[2] = {(cuuint64_t)(K / 64), (cuuint64_t)N};
-    const cuuint64_t strides[1] = {(cuuint64_t)(K / 64) * 2};
-    const cuuint32_t box[2] = {8, (cuuint32_t)rows};
-    const cuuint32_t es[2] = {1, 1};
-    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+    const cuuint64_t dims[4] = {(cuuint64_t)(K / 64), (cuuint64_t)N, (cuuint64_t)T, (cuuint64_t)S};
+    const cuuint64_t strides[3] = {(cuuint64_t)(K / 64) * 2, (cuuint64_t)(T > 1 ? tstride : 16),
+                                   (cuuint64_t)(S > 1 ? sstride : 16)};
+    const cuuint32_t box[4] = {8, (cuuint32_t)rows, (cuuint32_t)T, (cuuint32_t)S};
+    r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   }
@@ -445,20 +459,44 @@ bool qmv2_supported(int M, int K, int bits, int group_size, const pie_qmv_seg* s
   return encode_fn() != nullptr;
 }
 
+// a usable stride between two arrays: positive, a multiple of 16 bytes, below 2^40
+static bool stride_ok(const void* lo, const void* hi, long long* out) {
+  const long long d = (const char*)hi - (const char*)lo;
+  *out = d;
+  return d > 0 && d % 16 == 0 && d < (1ll << 40);
+}
+static const bool kNoStack = getenv("PIE_QMV2_NOSTACK") && atoi(getenv("PIE_QMV2_NOSTACK"));
+
 // Fill the matrix part of a descriptor (maps, tiling).  Returns false when a tensor map cannot be encoded.
-static bool fill_matrix(CUtensorMap* wmap, CUtensorMap* smap, CUtensorMap* bmap, int* N, int* tile0, int* out_off,
-                        int& ntiles, const pie_qmv_seg* segs, int nseg, int K, int dual) {
+static bool fill_matrix(Qmv2Args& a, const pie_qmv_seg* segs, int nseg, int K, int dual) {
   int tile = 0, off = 0;
+  const int rows = dual ? 8 : 16;
+  // biases a fixed stride behind the scales (the same stride for both matrices of a dual pair)?
+  long long sbs = 0, ws = 0, ss = 0, t = 0;
+  bool sb = !kNoStack, gu = dual && !kNoStack;
+  for (int i = 0; i < nseg && sb; ++i) {
+    sb = stride_ok(segs[i].scales, segs[i].biases, &t) && (i == 0 || !dual || t == sbs);
+    if (i == 0) sbs = t;
+  }
+  if (dual) {
+    gu = gu && sb && nseg == 2 && segs[0].N == segs[1].N && stride_ok(segs[0].wq, segs[1].wq, &ws) &&
+         stride_ok(segs[0].scales, segs[1].scales, &ss);
+    if (!gu) sb = false;   // (the stage layout of a pair needs both or neither)
+  }
+  a.sb_stacked = sb; a.gu_stacked = gu;
   for (int i = 0; i < nseg; ++i) {
-    const int rows = dual ? 8 : 16;
-    if (!get_map(&wmap[i], segs[i].wq, segs[i].N, K, rows, 0)) return false;
-    if (!get_map(&smap[i], segs[i].scales, segs[i].N, K, rows, 1)) return false;
-    if (!get_map(&bmap[i], segs[i].biases, segs[i].N, K, rows, 1)) return false;
-    N[i] = segs[i].N; tile0[i] = tile; out_off[i] = off;
+    if (!(gu && i == 1)) {
+      long long sbi = 0;
+      if (sb) stride_ok(segs[i].scales, segs[i].biases, &sbi);
+      if (!get_map(&a.wmap[i], segs[i].wq, segs[i].N, K, rows, 0, gu ? 2 : 1, ws, 1, 0)) return false;
+      if (!get_map(&a.smap[i], segs[i].scales, segs[i].N, K, rows, 1, gu ? 2 : 1, ss, sb ? 2 : 1, sbi)) return false;
+      if (!sb && !get_map(&a.bmap[i], segs[i].biases, segs[i].N, K, rows, 1, 1, 0, 1, 0)) return false;
+    }
+    a.N[i] = segs[i].N; a.tile0[i] = tile; a.out_off[i] = off;
     tile += (segs[i].N + 15) / 16;
     off += segs[i].N;
   }
-  ntiles = dual ? (segs[0].N + 7) / 8 : tile;
+  a.ntiles = dual ? (segs[0].N + 7) / 8 : tile;
   return true;
 }
 
@@ -467,13 +505,16 @@ int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld,
                     const pie_tp_fused* tp) {
   memset(&a, 0, sizeof(a));
   const int dual = epilogue == EPI_SILUMUL;
-  if (!fill_matrix(a.wmap, a.smap, a.bmap, a.N, a.tile0, a.out_off, a.ntiles, segs, nseg, K, dual)) return PIE_EUNSUPPORTED;
+  if (!fill_matrix(a, segs, nseg, K, dual)) return PIE_EUNSUPPORTED;
   a.nseg = nseg; a.dual = dual; a.M = M; a.K = K; a.upt = q2_kpad(K) / kQ2UnitK;
   a.x = (const uint16_t*)x; a.x_ld = x_ld;
   a.norm_w = (const uint16_t*)norm_weight; a.eps = eps;
   a.out = (uint16_t*)out; a.out_ld = out_ld; a.residual = (const uint16_t*)residual; a.epi = epilogue;
   // fp16 staging of x (see q2_stage_x) needs every block of a thread in registers: M * kpad / 16 <= 4 * 512 blocks
   static const int f16_env = getenv("PIE_QMV2_F16") ? atoi(getenv("PIE_QMV2_F16")) : -1;
+  static const int dbg_env = getenv("PIE_QMV2_DBG") ? atoi(getenv("PIE_QMV2_DBG")) : 0;  // experiments, see the kernel
+  a.dbg = dbg_env;
+  a.upt_inv = a.upt > 1 ? (uint32_t)(((1ull << 32) + a.upt - 1) / a.upt) : 0u;   // (upt == 1 is special-cased)
   // fp16 staging (see q2_stage_x) needs every block of a thread in registers.  Measured on B200, one row, us bf16 / fp16
   // staging: q/k/v 8.0 / 7.7, gate+up 17.4 / 16.5, head 52.2 / 49.7 (inputs that are RMS-normalised on the way in: the scale
   // comes out of the same reduction pass), o 5.3 / 5.7, down 11.5 / 11.6 (plain inputs: the row maximum is an extra pass).
@@ -498,12 +539,22 @@ int build_qmv2_args(Qmv2Args& a, void* out, int out_ld, const void* x, int x_ld,
   return PIE_OK;
 }
 
+// profiling aid: every launch takes the next slot of 256 CTAs x 16 stamps from the buffer set by pie_debug_stamps
+static unsigned long long* g_stamp_buf = nullptr;
+static size_t g_stamp_slots = 0, g_stamp_next = 0;
+void debug_stamps(void* buf, size_t bytes) {
+  g_stamp_buf = (unsigned long long*)buf; g_stamp_slots = buf ? bytes / kStampSlotBytes : 0; g_stamp_next = 0;
+}
+unsigned long long* next_stamp_slot() {
+  if (!g_stamp_buf || g_stamp_next >= g_stamp_slots) return nullptr;
+  return g_stamp_buf + (g_stamp_next++) * (kStampSlotBytes / 8);
+}
+
 template <bool ONECOL, bool F16, bool DUAL>
 static cudaError_t launch_qmv2_t(const Qmv2Args& a, bool pdl, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(qmv2_kernel<ONECOL, F16, DUAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, kQmvMaxSmem);
   if (e != cudaSuccess) return e;
-  int grid = num_sms();
-  if (grid > a.ntiles) grid = a.ntiles;
+  const int grid = a.tiles_q > 0 ? num_sms() : a.ntiles;   // (launch_qmv2 set the partition for this grid)
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid, 1, 1);
   cfg.blockDim = dim3(kQ2Warps * 32, 1, 1);
@@ -522,7 +573,15 @@ static cudaError_t launch_qmv2_d(const Qmv2Args& a, bool pdl, cudaStream_t st) {
   return a.dual ? launch_qmv2_t<ONECOL, F16, true>(a, pdl, st) : launch_qmv2_t<ONECOL, F16, false>(a, pdl, st);
 }
 
-cudaError_t launch_qmv2(const Qmv2Args& a, bool pdl, cudaStream_t st) {
+cudaError_t launch_qmv2(const Qmv2Args& a0, bool pdl, cudaStream_t st) {
+  Qmv2Args a = a0;
+  a.stamps = next_stamp_slot();
+  {
+    int grid = num_sms();
+    if (grid > a.ntiles) grid = a.ntiles;
+    a.tiles_q = a.ntiles / grid; a.tiles_r = a.ntiles % grid;
+    if (grid == a.ntiles) { a.tiles_q = 0; a.tiles_r = a.ntiles; }   // one tile per CTA, grid = ntiles (see launch_qmv2_t)
+  }
   if (a.f16) return a.M == 1 ? launch_qmv2_d<true, true>(a, pdl, st) : launch_qmv2_d<false, true>(a, pdl, st);
   return a.M == 1 ? launch_qmv2_d<true, false>(a, pdl, st) : launch_qmv2_d<false, false>(a, pdl, st);
 }

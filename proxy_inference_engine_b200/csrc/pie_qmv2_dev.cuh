@@ -24,6 +24,13 @@ __device__ __forceinline__ void tma_load_2d_b(uint32_t dst, const void* map, uin
       " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(pol)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* map, uint32_t bar, int c0, int c1, int c2, int c3,
+                                            uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(pol)
+      : "memory");
+}
 __device__ __forceinline__ void mbar_expect_tx_s(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
@@ -107,6 +114,37 @@ constexpr int kQ2VarOff = kQ2RedOff + 1024;
 __host__ __device__ inline int q2_kpad(int K) { return (K + kQ2UnitK - 1) / kQ2UnitK * kQ2UnitK; }
 __host__ __device__ inline int q2_xrow_bytes(int K) { return q2_kpad(K) * 2 + 16; }
 __host__ __device__ inline int q2_gpitch(int K) { return q2_kpad(K) / kGroup + 8; }  // bf16 elements per pieces row
+
+// ------------------------------------------------------------------------------------------- unit copies
+// One unit (16 rows x 512 k: 4096 B of packed weights, 256 B of scales, 256 B of biases) into a stage: 2 copies when the
+// arrays are co-located (see Qmv2Args), up to 6 otherwise.  d: the matrix's scalars, a: where its maps live.
+__device__ __forceinline__ void q2_issue_unit(const Qmv2Args& d, const Qmv2Args& a, int tile, int kc, uint32_t wd, uint32_t sd,
+                                              uint32_t bar, uint64_t pol) {
+  mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
+  if (d.dual) {
+    const int r0 = tile * 8;
+    if (d.gu_stacked) {
+      tma_load_4d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, 0, pol);
+      tma_load_4d(sd, &a.smap[0], bar, 8 * kc, r0, 0, 0, pol);
+      if (!d.sb_stacked) tma_load_4d(sd + 256, &a.bmap[0], bar, 8 * kc, r0, 0, 0, pol);
+    } else {
+      tma_load_4d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, 0, pol);
+      tma_load_4d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, 0, pol);
+      tma_load_4d(sd, &a.smap[0], bar, 8 * kc, r0, 0, 0, pol);
+      tma_load_4d(sd + 128, &a.smap[1], bar, 8 * kc, r0, 0, 0, pol);
+      tma_load_4d(sd + 256, &a.bmap[0], bar, 8 * kc, r0, 0, 0, pol);
+      tma_load_4d(sd + 384, &a.bmap[1], bar, 8 * kc, r0, 0, 0, pol);
+    }
+  } else {
+    int si = 0;
+    if (d.nseg > 1 && tile >= d.tile0[1]) si = 1;
+    if (d.nseg > 2 && tile >= d.tile0[2]) si = 2;
+    const int r0 = (tile - d.tile0[si]) * 16;
+    tma_load_4d(wd, &a.wmap[si], bar, 0, r0, 2 * kc, 0, pol);
+    tma_load_4d(sd, &a.smap[si], bar, 8 * kc, r0, 0, 0, pol);
+    if (!d.sb_stacked) tma_load_4d(sd + 256, &a.bmap[si], bar, 8 * kc, r0, 0, 0, pol);
+  }
+}
 
 // ------------------------------------------------------------------------------------------- x staging
 // x (optionally RMS-normalised: mx.fast.rms_norm, MLX/mlx/fast.cpp:93-111) -> shared memory in B-fragment order:
@@ -348,23 +386,30 @@ __device__ __forceinline__ void q2_stage_x_impl(const Qmv2Args& a, uint8_t* var,
   }
 }
 
-// One row, fp16 staging, every block of a thread in registers: ONE CTA barrier inside (the general form below needs four).
-// The first pass yields both reductions at once -- sum of squares for the RMS norm and max |x * w| -- and every warp then
-// reduces the 16 per-warp partials itself (same tree everywhere: identical, deterministic).  The row scale comes from the
-// bound  max |v| <= max |x w| * inv_rms * (1 + 2^-8)^2  on the twice-rounded normalised values v: the scaled maximum
-// lands in [2^13, 2^15), still exact in fp16.
-template <int MAXU>
-__device__ __forceinline__ void q2_stage_x1(const Qmv2Args& a, uint8_t* var, float* red) {
+// One activation row (the decode step), all 16 warps busy: a thread owns chunks of 8 consecutive k (16 bytes of x), the
+// two threads of a 16-k block swap halves so that each stores 16 contiguous bytes of the fragment order, the 8 threads of
+// a 64-k group add up its sums.  With the RMS norm and / or fp16 staging there is ONE CTA barrier inside: the first pass
+// yields both reductions at once -- sum of squares and max |x * w| -- and every thread then adds the 16 per-warp partials
+// itself (same order everywhere: identical, deterministic).  The row scale comes from the bound
+//   max |v| <= max |x w| * inv_rms * (1 + 2^-8)^2   on the twice-rounded normalised values v
+// so the scaled maximum lands in [2^13, 2^15), still exact in fp16.
+// MAXC > 0: a thread's chunks stay in registers between the passes (K <= 4096 * MAXC); MAXC == 0: any K, x is read twice.
+// The code is deliberately small (a launch runs it once, cold).
+template <bool F16, int MAXC, class AfterLoads>
+__device__ __forceinline__ void q2_stage_row(const Qmv2Args& a, uint8_t* var, float* red, AfterLoads after_loads,
+                                             unsigned long long* tr = nullptr) {
+  auto stamp = [&](int i) {   // profiling aid (one thread)
+    if (tr) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); tr[i] = t_; }
+  };
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int NT = kQ2Warps * 32;
+  constexpr int NC = MAXC > 0 ? MAXC : 1;
   const int kpad = q2_kpad(a.K), G = kpad / kGroup, gp = q2_gpitch(a.K);
   float* nsx = reinterpret_cast<float*>(var);
   uint16_t* pieces = reinterpret_cast<uint16_t*>(var + (size_t)G * 16);
   uint8_t* xs = var + (size_t)G * 16 + (((size_t)3 * gp * 2 + 15) & ~(size_t)15);
-  const int bpr = kpad / 16;
+  const int nchunks = a.K / 8;   // K is a multiple of 512
   const bool norm = a.norm_w != nullptr;
-  uint4 xb[MAXU][2], wb[MAXU][2];
-  float ss = 0.f, amax = 0.f;
   // Consumer side of a fused tensor-parallel exchange: every rank's o / down projection pushed its partial row into
   // slot r of this rank's buffer (pie_comm.cu has the layout); wait for the `world` flags of this exchange, then
   // x = residual + bf16(sum of the slots in rank order) -- the all_sum + `h + r` of the reference, in the x load.
@@ -378,111 +423,144 @@ __device__ __forceinline__ void q2_stage_x1(const Qmv2Args& a, uint8_t* var, flo
                     ((size_t)tp_set * a.tp_world + tid) * kTpMaxCtas, e);
     __syncthreads();
   }
+  auto load_x = [&](int c) -> uint4 {
+    uint4 xv = ldcg128(a.x + (size_t)c * 8);
+    if (tp) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const uint16_t* mine = reinterpret_cast<const uint16_t*>(a.tp_peer[a.tp_rank]) +
+                             (size_t)tp_set * a.tp_world * a.tp_max_elems + (size_t)c * 8;
+      for (int r = 0; r < a.tp_world; ++r) {
+        const uint4 pv = ldcg128(mine + (size_t)r * a.tp_max_elems);
+        const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
-  for (int u = 0; u < MAXU; ++u) {
-    const int b = u * NT + tid;
-    xb[u][0] = xb[u][1] = wb[u][0] = wb[u][1] = make_uint4(0, 0, 0, 0);
-    if (b < bpr && b * 16 < a.K) {
-      const uint4* src = reinterpret_cast<const uint4*>(a.x + b * 16);
-      xb[u][0] = ldcg128(src); xb[u][1] = ldcg128(src + 1);
-      if (norm) {
-        const uint4* wp = reinterpret_cast<const uint4*>(a.norm_w + b * 16);
-        wb[u][0] = __ldg(wp); wb[u][1] = __ldg(wp + 1);
+        for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16lo(pw[j]); acc[2 * j + 1] += bf16hi(pw[j]); }
       }
-      if (tp) {
-        float acc[16];
+      const uint32_t hw[4] = {xv.x, xv.y, xv.z, xv.w};
+      uint32_t o[4];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-        const uint16_t* mine = reinterpret_cast<const uint16_t*>(a.tp_peer[a.tp_rank]) +
-                               (size_t)tp_set * a.tp_world * a.tp_max_elems + b * 16;
-        for (int r = 0; r < a.tp_world; ++r) {
-          const uint4 p0 = ldcg128(mine + (size_t)r * a.tp_max_elems), p1 = ldcg128(mine + (size_t)r * a.tp_max_elems + 8);
-          const uint32_t pw[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16(bf16lo(hw[j]) + bfround(acc[2 * j]), bf16hi(hw[j]) + bfround(acc[2 * j + 1]));
+      xv = make_uint4(o[0], o[1], o[2], o[3]);
+      if (blockIdx.x == 0 && a.tp_h_out)   // the new residual stream, for the next exchange's consumer
+        *reinterpret_cast<uint4*>(a.tp_h_out + (size_t)c * 8) = xv;
+    }
+    return xv;
+  };
+  uint4 xb[NC], wb[NC];
+  float inv = 1.f, sc = 1.f;
+  {
+    float ss = 0.f, amax = 0.f;
+    auto reduce_chunk = [&](const uint4& xv, const uint4& wv) {
+      const uint32_t x4[4] = {xv.x, xv.y, xv.z, xv.w}, w4[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { acc[2 * j] += bf16lo(pw[j]); acc[2 * j + 1] += bf16hi(pw[j]); }
+      for (int j = 0; j < 4; ++j) {
+        const float lo = bf16lo(x4[j]), hi = bf16hi(x4[j]);
+        ss = fmaf(lo, lo, ss); ss = fmaf(hi, hi, ss);
+        if (norm) amax = fmaxf(amax, fmaxf(fabsf(lo * bf16lo(w4[j])), fabsf(hi * bf16hi(w4[j]))));
+        else amax = fmaxf(amax, fmaxf(fabsf(lo), fabsf(hi)));
+      }
+    };
+    if (MAXC > 0) {
+#pragma unroll
+      for (int u = 0; u < NC; ++u) {
+        const int c = u * NT + tid;
+        xb[u] = wb[u] = make_uint4(0, 0, 0, 0);
+        if (c < nchunks) {
+          xb[u] = load_x(c);
+          if (norm) wb[u] = __ldg(reinterpret_cast<const uint4*>(a.norm_w) + c);
         }
-        const uint32_t hw[8] = {xb[u][0].x, xb[u][0].y, xb[u][0].z, xb[u][0].w, xb[u][1].x, xb[u][1].y, xb[u][1].z, xb[u][1].w};
-        uint32_t o[8];
+      }
+      after_loads();
+      if (norm || F16) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          o[j] = pack_bf16(bf16lo(hw[j]) + bfround(acc[2 * j]), bf16hi(hw[j]) + bfround(acc[2 * j + 1]));
-        xb[u][0] = make_uint4(o[0], o[1], o[2], o[3]);
-        xb[u][1] = make_uint4(o[4], o[5], o[6], o[7]);
-        if (blockIdx.x == 0 && a.tp_h_out) {   // the new residual stream, for the next exchange's consumer
-          uint4* dst = reinterpret_cast<uint4*>(a.tp_h_out + b * 16);
-          dst[0] = xb[u][0]; dst[1] = xb[u][1];
+        for (int u = 0; u < NC; ++u) reduce_chunk(xb[u], wb[u]);
+      }
+      stamp(9 + (ss == 123456.f));
+    } else {
+      after_loads();
+      if (norm || F16) {
+        for (int c = tid; c < nchunks; c += NT) {
+          const uint4 xv = load_x(c);
+          uint4 wv = make_uint4(0, 0, 0, 0);
+          if (norm) wv = __ldg(reinterpret_cast<const uint4*>(a.norm_w) + c);
+          reduce_chunk(xv, wv);
         }
       }
     }
-  }
+    if (norm || F16) {
+      ss = warp_sum(ss);
+      amax = warp_max(amax);
+      if (lane == 0) { red[warp] = ss; red[32 + warp] = amax; }
+      __syncthreads();
+      float tot = 0.f, mx = 0.f;
+      stamp(10 + (red[0] == 123456.f));
 #pragma unroll
-  for (int u = 0; u < MAXU; ++u) {
-    const uint32_t x8[8] = {xb[u][0].x, xb[u][0].y, xb[u][0].z, xb[u][0].w, xb[u][1].x, xb[u][1].y, xb[u][1].z, xb[u][1].w};
-    const uint32_t w8[8] = {wb[u][0].x, wb[u][0].y, wb[u][0].z, wb[u][0].w, wb[u][1].x, wb[u][1].y, wb[u][1].z, wb[u][1].w};
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float lo = bf16lo(x8[j]), hi = bf16hi(x8[j]);
-      ss += lo * lo + hi * hi;
-      if (norm) amax = fmaxf(amax, fmaxf(fabsf(lo * bf16lo(w8[j])), fabsf(hi * bf16hi(w8[j]))));
-      else amax = fmaxf(amax, fmaxf(fabsf(lo), fabsf(hi)));
+      for (int w4 = 0; w4 < kQ2Warps / 4; ++w4) {
+        const float4 sv = *reinterpret_cast<const float4*>(red + 4 * w4), mv = *reinterpret_cast<const float4*>(red + 32 + 4 * w4);
+        tot += sv.x; tot += sv.y; tot += sv.z; tot += sv.w;
+        mx = fmaxf(fmaxf(mx, mv.x), fmaxf(fmaxf(mv.y, mv.z), mv.w));
+      }
+      if (norm) { inv = 1.0f / sqrtf(tot / (float)a.K + a.eps); mx = mx * inv * 1.0079f; }
+      if (F16) {
+        const uint32_t ex = (__float_as_uint(mx) >> 23) & 0xffu;
+        const bool sane = ex >= 16 && ex < 255;
+        sc = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;
+        if (tid == 0) red[208] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;   // 1 / scale, read after the caller's barrier
+      }
     }
   }
-  ss = warp_sum(ss);
-  amax = warp_max(amax);
-  if (lane == 0) { red[warp] = ss; red[32 + warp] = amax; }
-  __syncthreads();
-  const float tot = warp_sum(lane < kQ2Warps ? red[lane] : 0.f);
-  float mx = warp_max(lane < kQ2Warps ? red[32 + lane] : 0.f);
-  const float inv = norm ? 1.0f / sqrtf(tot / (float)a.K + a.eps) : 1.f;
-  if (norm) mx = mx * inv * 1.0079f;
-  const uint32_t ex = (__float_as_uint(mx) >> 23) & 0xffu;
-  const bool sane = ex >= 16 && ex < 255;
-  const float sc = sane ? __uint_as_float((uint32_t)(127 + 14 + 127 - (int)ex) << 23) : 1.f;
-  if (tid == 0) red[208] = sane ? __uint_as_float((uint32_t)((int)ex - 14) << 23) : 1.f;   // 1 / scale, read after the caller's barrier
   const float sc16 = sc * 0.0625f;
+  stamp(11 + (sc16 == 123456.f));
+  // second pass: normalise, convert, store in fragment order, group sums
+  auto emit_chunk = [&](int c, const uint4& xv, const uint4& wv) {   // every lane of the warp calls this (c may be out of range)
+    const bool ok = c < nchunks;
+    const uint32_t x4[4] = {xv.x, xv.y, xv.z, xv.w}, w4[4] = {wv.x, wv.y, wv.z, wv.w};
+    float v[8];
 #pragma unroll
-  for (int u = 0; u < MAXU; ++u) {
-    const int b = u * NT + tid;
-    const bool ok = b < bpr;
-    const uint32_t x8[8] = {xb[u][0].x, xb[u][0].y, xb[u][0].z, xb[u][0].w, xb[u][1].x, xb[u][1].y, xb[u][1].z, xb[u][1].w};
-    const uint32_t w8[8] = {wb[u][0].x, wb[u][0].y, wb[u][0].z, wb[u][0].w, wb[u][1].x, wb[u][1].y, wb[u][1].z, wb[u][1].w};
-    float s = 0.f, sh = 0.f;
-    uint32_t h[8];  // fp16 pair (k = 2j, 2j + 1) as the MMA will see it: scaled, odd k also / 16
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float lo = bf16lo(x8[j]), hi = bf16hi(x8[j]);
+    for (int j = 0; j < 4; ++j) {
+      float lo = bf16lo(x4[j]), hi = bf16hi(x4[j]);
       if (norm) {
-        lo = bfround(bfround(lo * inv) * bf16lo(w8[j]));
-        hi = bfround(bfround(hi * inv) * bf16hi(w8[j]));
+        const uint32_t t1 = pack_bf16(lo * inv, hi * inv);
+        const uint32_t t2 = pack_bf16(bf16lo(t1) * bf16lo(w4[j]), bf16hi(t1) * bf16hi(w4[j]));
+        lo = bf16lo(t2); hi = bf16hi(t2);
       }
-      s += lo + hi;
-      __half2 hv = __floats2half2_rn(lo * sc, hi * sc16);
-      h[j] = *reinterpret_cast<uint32_t*>(&hv);
-      const float2 back = __half22float2(hv);
-      sh += back.x + back.y;
+      v[2 * j] = lo; v[2 * j + 1] = hi;
     }
+    float s = 0.f, sh = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += v[j];
+    // word j of this thread = the pair (k = 8 h + j, 8 h + j + 4), j < 4
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (F16) {
+        const float scj = (j & 1) ? sc16 : sc;   // odd k are pre-divided by 16 (their nibbles lift to 1024 + 16 q)
+        __half2 hv = __floats2half2_rn(v[j] * scj, v[j + 4] * scj);
+        w[j] = *reinterpret_cast<uint32_t*>(&hv);
+        const float2 back = __half22float2(hv);
+        sh += back.x + back.y;
+      } else {
+        w[j] = pack_bf16(v[j], v[j + 4]);
+      }
+    }
+    const int h = c & 1;
+    const uint32_t ra = __shfl_xor_sync(0xffffffffu, h ? w[0] : w[2], 1), rb = __shfl_xor_sync(0xffffffffu, h ? w[1] : w[3], 1);
+    float gs = F16 ? sh : s;   // what the accumulator's start value is built from
     s += __shfl_xor_sync(0xffffffffu, s, 1);
     s += __shfl_xor_sync(0xffffffffu, s, 2);
-    sh += __shfl_xor_sync(0xffffffffu, sh, 1);
-    sh += __shfl_xor_sync(0xffffffffu, sh, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (F16) {
+      gs += __shfl_xor_sync(0xffffffffu, gs, 1);
+      gs += __shfl_xor_sync(0xffffffffu, gs, 2);
+      gs += __shfl_xor_sync(0xffffffffu, gs, 4);
+    } else {
+      gs = s;
+    }
     if (ok) {
-      uint32_t o[8];
-#pragma unroll
-      for (int mm = 0; mm < 4; ++mm) {
-#pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int k0 = mm + 8 * hh, k1 = k0 + 4;
-          const uint32_t lo16 = (k0 & 1) ? (h[k0 >> 1] >> 16) : (h[k0 >> 1] & 0xffffu);
-          const uint32_t hi16 = (k1 & 1) ? (h[k1 >> 1] >> 16) : (h[k1 >> 1] & 0xffffu);
-          o[2 * mm + hh] = lo16 | (hi16 << 16);
-        }
-      }
-      uint4* dst = reinterpret_cast<uint4*>(xs + (size_t)b * 32);
-      dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-      dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-      if ((b & 3) == 0) {
-        const int grp = b >> 2;
-        const float n = -1024.f * sh;
+      *reinterpret_cast<uint4*>(xs + (size_t)c * 16) = h ? make_uint4(ra, w[2], rb, w[3]) : make_uint4(w[0], ra, w[1], rb);
+      if ((c & 7) == 0) {
+        const int grp = c >> 3;
+        const float n = (F16 ? -1024.f : -128.f) * gs;
         *reinterpret_cast<float4*>(nsx + grp * 4) = make_float4(n, n, n, n);
         const float hi = bfround(s), r1 = s - hi, mid = bfround(r1), lo = bfround(r1 - mid);
         pieces[0 * gp + grp] = (uint16_t)(__float_as_uint(hi) >> 16);
@@ -490,16 +568,37 @@ __device__ __forceinline__ void q2_stage_x1(const Qmv2Args& a, uint8_t* var, flo
         pieces[2 * gp + grp] = (uint16_t)(__float_as_uint(lo) >> 16);
       }
     }
+  };
+  if (MAXC > 0) {
+#pragma unroll
+    for (int u = 0; u < NC; ++u) {
+      if (u * NT >= nchunks) break;   // CTA-uniform
+      emit_chunk(u * NT + tid, xb[u], wb[u]);
+    }
+  } else {
+    for (int c0 = 0; c0 < nchunks; c0 += NT) {   // nchunks is a multiple of 64: whole warps are in or out of range
+      const int c = c0 + tid;
+      uint4 xv = make_uint4(0, 0, 0, 0), wv = make_uint4(0, 0, 0, 0);
+      if (c < nchunks) {
+        xv = load_x(c);
+        if (norm) wv = __ldg(reinterpret_cast<const uint4*>(a.norm_w) + c);
+      }
+      emit_chunk(c, xv, wv);
+    }
   }
 }
 
-template <bool ONECOL, bool F16>
-__device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, float* red, unsigned long long* tr = nullptr) {
-  const int nits = (a.M * (q2_kpad(a.K) / 16) + kQ2Warps * 32 - 1) / (kQ2Warps * 32);
-  if (ONECOL && F16 && nits <= 2) {   // the decode step's case: one barrier inside instead of four
-    if (nits <= 1) q2_stage_x1<1>(a, var, red); else q2_stage_x1<2>(a, var, red);
+struct Q2Nothing { __device__ void operator()() const {} };
+template <bool ONECOL, bool F16, class AfterLoads = Q2Nothing>
+__device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, float* red, AfterLoads after_loads = AfterLoads(),
+                                           unsigned long long* tr = nullptr) {
+  if (ONECOL) {   // the decode step's case
+    if (a.K <= 4096) q2_stage_row<F16, 1>(a, var, red, after_loads, tr);
+    else q2_stage_row<F16, 0>(a, var, red, after_loads, tr);
     return;
   }
+  after_loads();
+  const int nits = (a.M * (q2_kpad(a.K) / 16) + kQ2Warps * 32 - 1) / (kQ2Warps * 32);
   if (nits <= 1) q2_stage_x_impl<ONECOL, F16, 1>(a, var, red, tr);
   else if (nits <= 2) q2_stage_x_impl<ONECOL, F16, 2>(a, var, red, tr);
   else q2_stage_x_impl<ONECOL, F16, 4>(a, var, red, tr);

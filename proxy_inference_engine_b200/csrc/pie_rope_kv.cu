@@ -1,6 +1,6 @@
 // RoPE (mx.fast.rope, MLX/mlx/fast.cpp:353-511; kernels/rope.metal:6-47) and the KV-cache writes of
 // ReusableKVCache.update_and_fetch (PIE/cache/kv_cache/reusable.py:96-142).
-// theta = (pos + offset) * scale * (1 / freqs[i]) in fp32, accurate sincosf, one bf16 rounding at the store.
+// theta = (pos + offset) * scale * (1 / freqs[i]) in fp32, range-reduced sine / cosine (rope_sincos, pie_ptx.cuh), one bf16 rounding at the store.
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
 
@@ -34,7 +34,7 @@ __global__ void rope_kernel(uint16_t* out, const uint16_t* x, long long rows, in
   const int p = (int)(row % L);
   const float theta = ((float)p + (float)offset) * scale * rope_inv_freq(freqs, base, i, half);
   float s, c;
-  sincosf(theta, &s, &c);
+  rope_sincos(theta, &s, &c);
   const int i1 = traditional ? 2 * i : i, i2 = traditional ? 2 * i + 1 : i + half;
   const float x1 = bf16lo((uint32_t)xr[i1]), x2 = bf16lo((uint32_t)xr[i2]);
   o[i1] = f2bf(__fsub_rn(__fmul_rn(x1, c), __fmul_rn(x2, s)));
@@ -71,7 +71,7 @@ __global__ void rope_kv_append_kernel(uint16_t* q_out, const uint16_t* qkv, uint
   }
   const float theta = (float)p * (1.0f / freqs[i]);
   float s, c;
-  sincosf(theta, &s, &c);
+  rope_sincos(theta, &s, &c);
   const float x1 = bf16lo((uint32_t)src[i]), x2 = bf16lo((uint32_t)src[i + half]);
   const uint16_t o1 = f2bf(__fsub_rn(__fmul_rn(x1, c), __fmul_rn(x2, s)));
   const uint16_t o2 = f2bf(__fadd_rn(__fmul_rn(x1, s), __fmul_rn(x2, c)));

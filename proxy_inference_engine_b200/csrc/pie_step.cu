@@ -43,6 +43,7 @@ struct StepArgs {
   int B, Hq, Hkv, D, R, rg, nsplit;
   float scale_log2e;
   const float* freqs;
+  const float* rope_tab;   // optional [B][2][D / 2]: sin, cos of this step's rotary angles (pie_rope_table), else computed here
   int32_t* pos;
   float* attn_part;        // [B * Hq][nsplit][D + 2]
   unsigned int* attn_cnt;  // [B * Hkv * rg]
@@ -119,6 +120,15 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, int rank) {
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
   return v;
 }
+// One 4-byte remote store into CTA `rank`'s shared memory that also counts 4 bytes on that CTA's mbarrier: the data is
+// visible to whoever sees the barrier's phase complete -- no fence, no cluster-wide barrier (st.async, sm_90+).
+__device__ __forceinline__ void st_async_f32(uint32_t local_addr, uint32_t local_bar, int rank, float v) {
+  uint32_t ra, rb;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(rank));
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(local_bar), "r"(rank));
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(ra), "f"(v), "r"(rb)
+               : "memory");
+}
 __device__ __forceinline__ size_t step_kv_addr(const KvLayout& kv, int b, int h, int t) {
   if (kv.page_table) {
     const int page = __ldg(kv.page_table + (size_t)b * kv.pt_stride + t / kv.page_size);
@@ -165,9 +175,20 @@ __device__ __forceinline__ void rope_row(float* v, const float* sn, const float*
 // CLUSTER: the splits of one (row, kv head, head group) are the CTAs of one thread-block cluster (stand-alone launch,
 // nsplit <= 8): their partials meet through distributed shared memory behind a cluster barrier instead of a global
 // workspace + fence + atomic + re-read, and every CTA of the cluster finishes a slice of the output.
-template <int D, int R, bool CLUSTER, int NW>
-__device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag) {
+template <int D, int R, bool CLUSTER, int NW, bool PREWAIT = false>
+__device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag,
+                                        unsigned long long* st = nullptr, uint64_t* cl_bar = nullptr) {
   constexpr int C = D / 64, E = 8 * C, PW = D + 2;
+  auto stamp = [&](int i) { if (st && threadIdx.x == 0) st[i] = globaltimer_ns(); };
+  if (CLUSTER && s.nsplit > 1) {
+    // the cluster's first CTA collects the other splits' partials: R * (D + 2) floats each, counted by its mbarrier
+    if (blockIdx.x % s.nsplit == 0 && threadIdx.x == 0) {
+      mbar_init(cl_bar, 1);
+      mbar_arrive_expect_tx(cl_bar, (uint32_t)(s.nsplit - 1) * R * PW * 4);
+      fence_mbar_init();
+    }
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // waited for just before the pushes
+  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, tg = lane >> 3;
   const int units = s.B * s.Hkv * s.rg * s.nsplit;
   const int qkv_ld = (s.Hq + 2 * s.Hkv) * D;
@@ -178,25 +199,63 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
     const int kvh = rest % s.Hkv;
     const int b = rest / s.Hkv;
     const int qh0 = kvh * (s.rg * R) + rgi * R;
-    // everything that does not depend on the position is requested first: one round trip for pos, freqs and q
+    // Everything that depends only on the POSITION comes first -- with PREWAIT (stand-alone launch) before the wait on the
+    // q/k/v projection: the rotation's sines, and the K/V rows of older tokens (written by earlier steps) of two rounds.
     const uint16_t* row = P.qkv + (size_t)b * qkv_ld;
+    float4 s0, s1, c0, c1;   // this lane's 8 sines and cosines, requested together with the position
+    s0 = s1 = c0 = c1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (s.rope_tab) {
+      const float4* tb = reinterpret_cast<const float4*>(s.rope_tab + (size_t)b * D + (C == 2 ? 8 * sub : 8 * (sub & 3)));
+      s0 = __ldg(tb); s1 = __ldg(tb + 1); c0 = __ldg(tb + D / 8); c1 = __ldg(tb + D / 8 + 1);
+    }
+    const int p = s.pos[b], ctx = p + 1;
+    const int per = (ctx + s.nsplit - 1) / s.nsplit;
+    const int t0 = split * per, t1 = min(ctx, t0 + per);
+    const size_t rec0 = ((size_t)b * s.Hq + qh0) * s.nsplit;
+    // K/V rows are requested two rounds ahead: kn / vn hold the next round, kn2 / vn2 the one after
+    uint4 kn[C], vn[C], kn2[C], vn2[C];
+    auto request_to = [&](uint4 (&kd)[C], uint4 (&vd)[C], int tb_, bool fresh_ok) {
+      const int t_ = tb_ + tg;
+      if (t_ < t1) {
+        const bool fresh_ = t_ == p;
+        if (fresh_ && !fresh_ok) return;
+        const size_t off = step_kv_addr(P.kv, b, kvh, t_);
+        const uint4* kp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + kvh) * D)
+                                 : reinterpret_cast<const uint4*>(P.kc + off);
+        const uint4* vp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + s.Hkv + kvh) * D)
+                                 : reinterpret_cast<const uint4*>(P.vc + off);
+#pragma unroll
+        for (int c = 0; c < C; ++c) { kd[c] = ldcg128(kp + sub + 8 * c); vd[c] = ldcg128(vp + sub + 8 * c); }
+      }
+    };
+    const int tb0 = t0 + warp * 4;
+    if (tb0 < t1) request_to(kn, vn, tb0, false);
+    if (tb0 + NW * 4 < t1) request_to(kn2, vn2, tb0 + NW * 4, false);
+    float sn[8], cs[8];
+    stamp(1);
+    if (s.rope_tab) {
+      sn[0] = s0.x; sn[1] = s0.y; sn[2] = s0.z; sn[3] = s0.w; sn[4] = s1.x; sn[5] = s1.y; sn[6] = s1.z; sn[7] = s1.w;
+      cs[0] = c0.x; cs[1] = c0.y; cs[2] = c0.z; cs[3] = c0.w; cs[4] = c1.x; cs[5] = c1.y; cs[6] = c1.z; cs[7] = c1.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        rope_sincos((float)p * (1.0f / __ldg(s.freqs + (C == 2 ? 8 * sub : 8 * (sub & 3)) + j)), &sn[j], &cs[j]);
+    }
+    stamp(3);
+    if (PREWAIT) {
+      pdl_wait();
+      stamp(2);
+    }
     uint4 qraw[R][C];
-    float fr[8];
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
       for (int c = 0; c < C; ++c)
         qraw[r][c] = ldcg128(reinterpret_cast<const uint4*>(row + (size_t)(qh0 + r) * D) + sub + 8 * c);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) fr[j] = __ldg(s.freqs + (C == 2 ? 8 * sub : 8 * (sub & 3)) + j);
-    const int p = s.pos[b], ctx = p + 1;
-    const int per = (ctx + s.nsplit - 1) / s.nsplit;
-    const int t0 = split * per, t1 = min(ctx, t0 + per);
-    const size_t rec0 = ((size_t)b * s.Hq + qh0) * s.nsplit;
+    // the token of this step, if it falls into one of the two rounds requested before the projection was complete
+    if (tb0 + tg == p && tb0 + tg < t1) request_to(kn, vn, tb0, true);
+    if (tb0 + NW * 4 + tg == p && tb0 + NW * 4 + tg < t1) request_to(kn2, vn2, tb0 + NW * 4, true);
     if (t0 < t1) {
-      float sn[8], cs[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) sincosf((float)p * (1.0f / fr[j]), &sn[j], &cs[j]);
       float q[R][E];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -206,6 +265,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
 #pragma unroll
         for (int e = 0; e < E; ++e) q[r][e] *= s.scale_log2e;
       }
+      stamp(4 + (q[0][0] == 123456.f));
       float m[R], l[R], acc[R][E];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -213,23 +273,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[r][e] = 0.f;
       }
-      // K/V rows of the NEXT round are requested before the current round is used: one round trip hidden per round
-      uint4 kn[C], vn[C];
-      auto request = [&](int tb_) {
-        const int t_ = tb_ + tg;
-        if (t_ < t1) {
-          const bool fresh_ = t_ == p;
-          const size_t off = step_kv_addr(P.kv, b, kvh, t_);
-          const uint4* kp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + kvh) * D)
-                                   : reinterpret_cast<const uint4*>(P.kc + off);
-          const uint4* vp = fresh_ ? reinterpret_cast<const uint4*>(row + (size_t)(s.Hq + s.Hkv + kvh) * D)
-                                   : reinterpret_cast<const uint4*>(P.vc + off);
-#pragma unroll
-          for (int c = 0; c < C; ++c) { kn[c] = ldcg128(kp + sub + 8 * c); vn[c] = ldcg128(vp + sub + 8 * c); }
-        }
-      };
-      if (t0 + warp * 4 < t1) request(t0 + warp * 4);
-      for (int tb = t0 + warp * 4; tb < t1; tb += NW * 4) {  // warp-uniform trip count; tail lanes idle
+      for (int tb = tb0; tb < t1; tb += NW * 4) {  // warp-uniform trip count; tail lanes idle
         const int t = tb + tg;
         const bool ok = t < t1;
         float kf[E], vf[E];
@@ -238,8 +282,8 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
         const bool fresh = ok && t == p;  // the token of this step: not in the cache yet
         uint4 kr[C], vr[C];
 #pragma unroll
-        for (int c = 0; c < C; ++c) { kr[c] = kn[c]; vr[c] = vn[c]; }
-        if (tb + NW * 4 < t1) request(tb + NW * 4);
+        for (int c = 0; c < C; ++c) { kr[c] = kn[c]; vr[c] = vn[c]; kn[c] = kn2[c]; vn[c] = vn2[c]; }
+        if (tb + 2 * NW * 4 < t1) request_to(kn2, vn2, tb + 2 * NW * 4, true);
         if (ok) {
 #pragma unroll
           for (int c = 0; c < C; ++c) { unpack8(kr[c], &kf[8 * c]); unpack8(vr[c], &vf[8 * c]); }
@@ -280,6 +324,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
           }
         }
       }
+      stamp(5 + (l[0] == 123456.f));
       // merge the 4 token slots of the warp (lanes with equal `sub` hold the same feature slice)
 #pragma unroll
       for (int o = 8; o <= 16; o <<= 1) {
@@ -307,6 +352,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
       }
     }
     __syncthreads();
+    if (CLUSTER && s.nsplit > 1) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // the first CTA's mbarrier is set up
     // merge the warps; thread -> (r, d).  An empty split leaves (m, l) = (-inf, 0).
     for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
       const int r = i / D, d = i % D;
@@ -323,32 +369,43 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
       if (s.nsplit == 1) {
         P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
       } else if (CLUSTER) {
-        float* rec = scratch + (size_t)NW * R * PW + (size_t)r * PW;  // this CTA's partial, read by its cluster peers
-        rec[d] = at;
-        if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
+        // Splits 1.. push their partial into the slot `split` of the cluster's first CTA (remote shared memory; every
+        // store also counts on that CTA's mbarrier); the first CTA keeps its own in slot 0.
+        float* rec = scratch + (size_t)NW * R * PW + ((size_t)split * R + r) * PW;
+        if (split == 0) {
+          rec[d] = at;
+          if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
+        } else {
+          const uint32_t bar = smem_u32(cl_bar);
+          st_async_f32(smem_u32(rec + d), bar, 0, at);
+          if (d == 0) { st_async_f32(smem_u32(rec + D), bar, 0, mn); st_async_f32(smem_u32(rec + D + 1), bar, 0, lt); }
+        }
       } else {
         float* rec = s.attn_part + (rec0 + (size_t)r * s.nsplit + split) * PW;
         rec[d] = at;
         if (d == 0) { rec[D] = mn; rec[D + 1] = lt; }
       }
     }
+    stamp(6);
     if (CLUSTER && s.nsplit > 1) {
-      cluster_sync();  // release / acquire: every split's partial is in its CTA's shared memory
-      const uint32_t mine = smem_u32(scratch + (size_t)NW * R * PW);
-      for (int i = threadIdx.x * s.nsplit + split; i < R * D; i += blockDim.x * s.nsplit) {  // this CTA's slice
-        const int r = i / D, d = i % D;
-        float mn = -INFINITY;
-        for (int sp = 0; sp < s.nsplit; ++sp) mn = fmaxf(mn, ld_dsmem_f32(mine + (r * PW + D) * 4, sp));
-        float lt = 0.f, at = 0.f;
-        for (int sp = 0; sp < s.nsplit; ++sp) {  // split order: deterministic
-          const float ms = ld_dsmem_f32(mine + (r * PW + D) * 4, sp);
-          const float cw = ms == -INFINITY ? 0.f : exp2f(ms - mn);
-          lt += ld_dsmem_f32(mine + (r * PW + D + 1) * 4, sp) * cw;
-          at += ld_dsmem_f32(mine + (r * PW + d) * 4, sp) * cw;
+      if (split == 0) {
+        __syncthreads();        // slot 0 is written
+        mbar_wait(cl_bar, 0);   // every other split's R * (D + 2) values have landed
+        const float* part = scratch + (size_t)NW * R * PW;
+        for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
+          const int r = i / D, d = i % D;
+          float mn = -INFINITY;
+          for (int sp = 0; sp < s.nsplit; ++sp) mn = fmaxf(mn, part[((size_t)sp * R + r) * PW + D]);
+          float lt = 0.f, at = 0.f;
+          for (int sp = 0; sp < s.nsplit; ++sp) {  // split order: deterministic
+            const float* rec = part + ((size_t)sp * R + r) * PW;
+            const float cw = rec[D] == -INFINITY ? 0.f : exp2f(rec[D] - mn);
+            lt += rec[D + 1] * cw;
+            at += rec[d] * cw;
+          }
+          P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
         }
-        P.attn_out[((size_t)b * s.Hq + qh0 + r) * D + d] = f2bf(at / lt);
       }
-      cluster_sync();  // no CTA leaves (or reuses its partial) while a peer may still read it
     }
     if (!CLUSTER && s.nsplit > 1) {
       __threadfence();
@@ -443,11 +500,13 @@ constexpr int kAttnWarps = 8;  // stand-alone launch: 8 warps and up to 255 regi
 template <int D, int R, bool CLUSTER>
 __global__ void __launch_bounds__(kAttnWarps * 32, 1) attn_fused_kernel(const __grid_constant__ StepArgs s,
                                                                        const __grid_constant__ StepPhase P) {
-  __shared__ float scratch[(kAttnWarps + 1) * R * (D + 2)];
+  __shared__ float scratch[(kAttnWarps + 8) * R * (D + 2)];   // per-warp partials + (first CTA of a cluster) per-split partials
+  __shared__ uint64_t cl_bar;
   __shared__ int s_flag;
+  if (s.trace && threadIdx.x == 0) s.trace[blockIdx.x * 16] = globaltimer_ns();
   pdl_launch_dependents();
-  pdl_wait();
-  attn_phase<D, R, CLUSTER, kAttnWarps>(s, P, scratch, &s_flag);
+  attn_phase<D, R, CLUSTER, kAttnWarps, true>(s, P, scratch, &s_flag, s.trace ? s.trace + blockIdx.x * 16 : nullptr, &cl_bar);
+  if (s.trace && threadIdx.x == 0) s.trace[blockIdx.x * 16 + 7] = globaltimer_ns();
 }
 
 // ---- the one-launch step: TMA-fed GEMV phases (the arithmetic of pie_qmv2.cu, one row, fp16 staging) ---------------
@@ -517,24 +576,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) decode_step2_kernel(const __
   // d: the matrix's scalars (shared copy, or the plan itself for a matrix further ahead); a: the plan entry (maps)
   auto issue = [&](const Qmv2Args& d, const Qmv2Args& a, int tile, int kc, int st) {
     const uint32_t bar = bar0 + st * 8, wd = wst + st * kQ2WBytes, sd = sbst + st * kQ2SbBytes;
-    mbar_expect_tx_s(bar, kQ2WBytes + kQ2SbBytes);
-    if (d.dual) {
-      const int r0 = tile * 8;
-      tma_load_3d(wd, &a.wmap[0], bar, 0, r0, 2 * kc, pol);
-      tma_load_3d(wd + 2048, &a.wmap[1], bar, 0, r0, 2 * kc, pol);
-      tma_load_2d_b(sd, &a.smap[0], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 128, &a.smap[1], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 256, &a.bmap[0], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 384, &a.bmap[1], bar, 8 * kc, r0, pol);
-    } else {
-      int si = 0;
-      if (d.nseg > 1 && tile >= d.tile0[1]) si = 1;
-      if (d.nseg > 2 && tile >= d.tile0[2]) si = 2;
-      const int r0 = (tile - d.tile0[si]) * 16;
-      tma_load_3d(wd, &a.wmap[si], bar, 0, r0, 2 * kc, pol);
-      tma_load_2d_b(sd, &a.smap[si], bar, 8 * kc, r0, pol);
-      tma_load_2d_b(sd + 256, &a.bmap[si], bar, 8 * kc, r0, pol);
-    }
+    q2_issue_unit(d, a, tile, kc, wd, sd, bar, pol);
   };
   int cur_phase = 0;  // the matrix being consumed: ph[] holds cur_phase and cur_phase + 1
   auto desc_of = [&](int q) -> const Qmv2Args& {
@@ -602,7 +644,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) decode_step2_kernel(const __
     gbar();
     if (tracing) s.trace[2 + 3 * p] = globaltimer_ns();
     if (lane == 0) { edge_tile[warp * 2] = -1; edge_tile[warp * 2 + 1] = -1; }
-    q2_stage_x<true, true>(a, var, red, tracing && s.trace_stage ? s.trace_stage + 4 * p : nullptr);
+    q2_stage_x<true, true>(a, var, red);   // (the staging's own stamps belong to the stand-alone launch's 16-stamp slots)
     __syncthreads();
     if (tracing) s.trace[3 + 3 * p] = globaltimer_ns();
     top_up(p);
@@ -881,9 +923,30 @@ int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, 
   return PIE_OK;
 }
 
+// sin / cos of the rotary angles of positions[b], once per step instead of once per layer and lane
+__global__ void rope_table_kernel(float* table, const int32_t* pos, const float* freqs, int half) {
+  const int b = blockIdx.x;
+  const float p = (float)pos[b];
+  for (int j = threadIdx.x; j < half; j += blockDim.x) {
+    float sn, cs;
+    rope_sincos(p * (1.0f / freqs[j]), &sn, &cs);
+    table[(size_t)b * 2 * half + j] = sn;
+    table[(size_t)b * 2 * half + half + j] = cs;
+  }
+}
+
+int pie_rope_table(float* table, const int32_t* positions, const float* freqs, int B, int half_dims, void* stream) {
+  if (B == 0) return PIE_OK;
+  if (!table || !positions || !freqs) return PIE_ENULL;
+  if (B < 0 || half_dims <= 0) return PIE_EINVAL_SHAPE;
+  count_launch();
+  rope_table_kernel<<<B, 64, 0, (cudaStream_t)stream>>>(table, positions, freqs, half_dims);
+  return status_of(cudaGetLastError());
+}
+
 int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache, const pie_kv_layout* kv,
-                          const int32_t* positions, const float* freqs, int B, int Hq, int Hkv, int D, float scale,
-                          int nsplit, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
+                          const int32_t* positions, const float* freqs, const float* rope_table, int B, int Hq, int Hkv,
+                          int D, float scale, int nsplit, void* workspace, size_t workspace_bytes, int pdl, void* stream) {
   if (B == 0) return PIE_OK;
   if (!out || !qkv || !kcache || !vcache || !kv || !positions || !freqs) return PIE_ENULL;
   if (B < 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return PIE_EINVAL_SHAPE;
@@ -902,13 +965,14 @@ int pie_decode_attn_fused(void* out, const void* qkv, void* kcache, void* vcache
   memset(&P, 0, sizeof(P));
   s.B = B; s.Hq = Hq; s.Hkv = Hkv; s.D = D; s.R = R; s.rg = n_rep / R; s.nsplit = nsplit;
   s.scale_log2e = scale * 1.4426950408889634f;
-  s.freqs = freqs; s.pos = const_cast<int32_t*>(positions);
+  s.freqs = freqs; s.pos = const_cast<int32_t*>(positions); s.rope_tab = rope_table;
   const size_t cnt_bytes = (((size_t)B * Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
   s.attn_cnt = reinterpret_cast<unsigned int*>(workspace);
   s.attn_part = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + cnt_bytes) : nullptr;
   P.qkv = (const uint16_t*)qkv; P.attn_out = (uint16_t*)out; P.kc = (uint16_t*)kcache; P.vc = (uint16_t*)vcache;
   P.kv.batch_stride = kv->batch_stride; P.kv.head_stride = kv->head_stride; P.kv.tok_stride = kv->tok_stride;
   P.kv.page_table = kv->page_table; P.kv.pt_stride = kv->pt_stride; P.kv.page_size = kv->page_size;
+  s.trace = (B * Hkv * s.rg * nsplit <= 256) ? next_stamp_slot() : nullptr;   // profiling aid (pie_debug_stamps)
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(B * Hkv * s.rg * nsplit), 1, 1);
   cfg.blockDim = dim3(kAttnWarps * 32, 1, 1);

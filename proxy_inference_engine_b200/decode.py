@@ -72,6 +72,7 @@ class DecodeEngine:
         self.attn = torch.empty((B, self.Hq * self.D), dtype=bf, device=dev)
         self.act = torch.empty((B, a.intermediate_size), dtype=bf, device=dev)
         self.logits = torch.empty((B, a.vocab_size), dtype=bf, device=dev)
+        self.rope_tab = torch.empty((B, 2, self.D // 2), dtype=torch.float32, device=dev)
         # tensor parallel (tp.py): this rank owns Hq/W query heads, Hkv/W kv heads, ffn/W columns and V/W logits
         self.tp = tp if tp is not None else getattr(model, "tp", None)
         self.tp_on = self.tp is not None and self.tp.on
@@ -144,6 +145,9 @@ class DecodeEngine:
             self.nsplit_fused = int(os.environ["PIE_ATTN_SPLITS"])
         nb = L.pie_decode_attn_workspace_bytes(B, self.Hq, self.D, max(self.nsplit, self.nsplit_fused))
         self.attn_ws = torch.zeros(max(nb, 256), dtype=torch.uint8, device=dev)
+        if os.environ.get("PIE_COLOCATE", "1") != "0":
+            from .checkpoint import colocate_for_decode
+            colocate_for_decode(model)   # fewer TMA copies per weight tile (see checkpoint.colocate_for_decode)
         # per-layer segment tables (host structs must outlive the captured graph: keep references)
         self.seg_qkv, self.seg_o, self.seg_gu, self.seg_down = [], [], [], []
         nb = 0
@@ -247,6 +251,9 @@ class DecodeEngine:
         h, hid = self.h, a.hidden_size
         _lib.check(L.pie_dequantize(_p(h), _p(emb.weight), _p(emb.scales), _p(emb.biases), _p(self.tokens), self.B,
                                     emb.weight.shape[0], hid, self.gs, self.bits, _stream()), "embed")
+        if self.attn_fused:   # this step's rotary sines, once for all layers
+            _lib.check(L.pie_rope_table(_p(self.rope_tab), _p(self.positions), _p(m.layers[0].self_attn.rope._freqs),
+                                        self.B, self.D // 2, _stream()), "rope_table")
         qd = self.Hq * self.D
         import os
         skip = set(filter(None, os.environ.get("PIE_DEBUG_SKIP", "").split(",")))  # tools/bench_step_parts.py only
@@ -262,7 +269,8 @@ class DecodeEngine:
             if "attn" not in skip and self.attn_fused:
                 _lib.check(L.pie_decode_attn_fused(_p(self.attn), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                                    C.byref(self.lay[i]), _p(self.positions),
-                                                   _p(ly.self_attn.rope._freqs), self.B, self.Hq, self.Hkv, self.D,
+                                                   _p(ly.self_attn.rope._freqs), _p(self.rope_tab), self.B, self.Hq,
+                                                   self.Hkv, self.D,
                                                    float(ly.self_attn.scale), self.nsplit_fused, _p(self.attn_ws),
                                                    self.attn_ws.numel(), self.pdl, _stream()), "decode_attn_fused")
             if "rope" not in skip and not self.attn_fused:

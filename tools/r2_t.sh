@@ -1,5 +1,3 @@
-#!/bin/bash
-OUT=gpurun_out/r2t
-mkdir -p $OUT
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/tp_check.py > $OUT/tp_check.log 2>&1; echo "tp_check exit $?" >> $OUT/tp_check.log; tail -5 $OUT/tp_check.log
-bash tools/r2_s.sh
+python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+python tools/timeline_step.py --layers 8 --dump gpurun_out/tl_h1.npy > gpurun_out/tl_h1.json 2>&1
+PIE_QMV2_DBG=8 python tools/timeline_step.py --layers 8 --dump gpurun_out/tl_h1d8.npy > gpurun_out/tl_h1d8.json 2>&1
