@@ -35,7 +35,8 @@ typedef enum pie_status {
   PIE_ECUDA = 4,         /* CUDA error; see pie_last_cuda_error()                          */
   PIE_ENULL = 5,         /* a required pointer is NULL                                    */
   PIE_EALIGN = 6,        /* a pointer is not 16-byte aligned                               */
-  PIE_EWORKSPACE = 7     /* caller-owned workspace missing or smaller than *_workspace_bytes() */
+  PIE_EWORKSPACE = 7,    /* caller-owned workspace missing or smaller than *_workspace_bytes() */
+  PIE_ESTATIC_LIMIT = 8  /* the request needs more than the library's static scratch (PIE_STATIC_SCRATCH_BYTES) */
 } pie_status;
 
 enum { PIE_DTYPE_BF16 = 0, PIE_DTYPE_F32 = 1 };
@@ -138,6 +139,19 @@ int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context);
 int pie_decode_attn(void* out, const void* q, const void* kcache, const void* vcache,
                     const pie_kv_layout* kv_host, const int32_t* positions, int B, int Hq, int Hkv, int D,
                     float scale, int nsplit, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- pie_decode_attn without a caller-owned workspace and without any allocation -------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * pie_decode_attn; the split counters and per-split partials live in a file-scope device array of
+ * PIE_STATIC_SCRATCH_BYTES (4 MiB), held by every GPU that loads the library until exit.  A request that needs more
+ * (pie_decode_attn_workspace_bytes(B, Hq, D, nsplit) > PIE_STATIC_SCRATCH_BYTES) returns PIE_ESTATIC_LIMIT and
+ * launches nothing.  All calls share the array: the counters are cleared on `stream` before each launch, and calls that
+ * overlap on the GPU (different streams without ordering) race -- serialise them or use pie_decode_attn.           */
+#define PIE_STATIC_SCRATCH_BYTES (4u << 20)
+int pie_decode_attn_static(void* out, const void* q, const void* kcache, const void* vcache,
+                           const pie_kv_layout* kv_host, const int32_t* positions, int B, int Hq, int Hkv, int D,
+                           float scale, int nsplit, void* stream);
 
 /* ---- a7+a8+a9 in one launch: rotate q and k at positions[b], append k,v to the cache, flash-decode ---------------
  * (Attention.__call__ PIE/models/llama/language.py:84-104 for L == 1).  qkv bf16 [B, (Hq + 2 Hkv) D] un-rotated, as

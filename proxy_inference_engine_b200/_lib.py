@@ -15,7 +15,7 @@ CSRC = os.path.join(_HERE, "csrc")
 
 PIE_OK = 0
 STATUS = {1: "EINVAL_SHAPE", 2: "EINVAL_DTYPE", 3: "EUNSUPPORTED", 4: "ECUDA", 5: "ENULL", 6: "EALIGN",
-          7: "EWORKSPACE"}
+          7: "EWORKSPACE", 8: "ESTATIC_LIMIT"}
 EPI_STORE, EPI_RESADD, EPI_SILUMUL = 0, 1, 2
 DTYPE_BF16, DTYPE_F32 = 0, 1
 
@@ -86,6 +86,7 @@ SIGNATURES = {
     "pie_decode_attn_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
     "pie_rope_table": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "pie_decode_attn_static": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp]),
     "pie_decode_attn_fused": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _vp,
                                    _sz, _i, _vp]),
     "pie_prefill_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _i, _i, _i, _i, _i, _i, _f, _vp]),

@@ -163,6 +163,7 @@ const char* pie_status_string(int s) {
     case PIE_ENULL: return "null pointer";
     case PIE_EALIGN: return "pointer not 16-byte aligned";
     case PIE_EWORKSPACE: return "workspace too small";
+    case PIE_ESTATIC_LIMIT: return "request exceeds the library's static scratch (PIE_STATIC_SCRATCH_BYTES = 4 MiB)";
     default: return "unknown";
   }
 }
