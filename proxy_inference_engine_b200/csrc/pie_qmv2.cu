@@ -62,6 +62,12 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                 \
     a.stamps[blockIdx.x * 16 + (i)] = t_;                                                  \
   }
+#define Q2_STAMP_ORDERED(i) /* not to be moved across the CTA barrier next to it */       \
+  if (a.stamps && tid == 0) {                                                              \
+    unsigned long long t_;                                                                 \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)::"memory");                       \
+    a.stamps[blockIdx.x * 16 + (i)] = t_;                                                  \
+  }
   Q2_STAMP(0)
 
   // ---- this CTA's tiles and this warp's run of units -------------------------------------------------
@@ -110,15 +116,20 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     edge_tile[warp * 2] = -1;
     edge_tile[warp * 2 + 1] = -1;
   }
-  // First loads: stage 0 before the dependency wait, stage 1 right behind the loads of x (measured: with both stages in
-  // flight before the wait, the 148 x 16 x 9 KB of weight traffic delays the x loads every CTA is about to wait for).
+  // First loads: stage 0 before the dependency wait, stage 1 right behind the loads of x.  Measured on the 8B step
+  // (tools/timeline_step.py, us per layer): this order 47.8-49.3; both stages before the wait 49.7 (when all CTAs of a
+  // launch start together -- gate/up behind o -- 148 x 16 x 9 KB of weight requests queue in front of the loads of x every
+  // CTA is about to wait for); both behind the loads of x 52.5 (the elected lane's copies -- cold descriptors -- then sit
+  // in every warp's staging path).  PIE_QMV2_DBG: 8 = both before the wait, 16 = both behind x, 4 = both after the staging.
   Q2_STAMP(8)
-  if (!(a.dbg & 4)) {
+  const int pf_mode = a.dbg & (4 | 8 | 16);
+  if (pf_mode == 0 || pf_mode == 8) {
     if (p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
-    if ((a.dbg & 8) && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+    if (pf_mode == 8 && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
   }
   auto after_x_loads = [&]() {
-    if (!(a.dbg & (4 | 8)) && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
+    if (pf_mode == 16 && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 0); advance(); }
+    if ((pf_mode == 0 || pf_mode == 16) && p_u < ue) { if (elect_one()) issue(p_tile, p_kc, 1); advance(); }
   };
   Q2_STAMP(1)
   pdl_launch_dependents();
@@ -337,7 +348,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   if (e0_tile >= 0 && (e0_tile + 1) * upt <= ue) fin_tile = e0_tile;   // edge 0 ends inside this run
   if (fin_tile >= 0 && a.epi == EPI_RESADD) load_residual(fin_tile);
   __syncthreads();
-  Q2_STAMP(6)
+  Q2_STAMP_ORDERED(6)
   if (fin_tile >= 0) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     for (int w2 = 0; w2 <= warp; ++w2) {
@@ -351,7 +362,7 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
     }
     epilogue(fin_tile, v);
   }
-  Q2_STAMP(7)
+  Q2_STAMP_ORDERED(7)
   if (ONECOL && a.tp_mode == 1) {
     // producer: when this rank's LAST CTA is done, every peer may read slot `tp_rank` of exchange tp_e
     // (one fence by one thread behind the CTA barrier -- cumulative over the CTA's pushes -- not one per thread)

@@ -26,7 +26,7 @@ struct Qmv2Args {
   // gu_stacked (dual): the up matrix lies a fixed stride behind the gate matrix (one copy brings both).  The engine
   // allocates its matrices that way (checkpoint.colocate_for_decode); other callers get one copy per array.
   int sb_stacked, gu_stacked;
-  int dbg;  // experiments (PIE_QMV2_DBG): 1 = skip the arithmetic, 4 = first loads after staging, 8 = both stages before it
+  int dbg;  // experiments (PIE_QMV2_DBG): 1 = skip the arithmetic, 4 / 8 / 16 = where the first loads are issued (see the kernel)
   int f16;  // 1: activations staged as scaled fp16, weights lifted to fp16 (see q2_stage_x)
   int N[kMaxSeg], tile0[kMaxSeg], out_off[kMaxSeg];
   uint32_t lift_mask, lift_mask2, lift_magic;

@@ -594,6 +594,7 @@ __device__ __forceinline__ void q2_stage_x(const Qmv2Args& a, uint8_t* var, floa
                                            unsigned long long* tr = nullptr) {
   if (ONECOL) {   // the decode step's case
     if (a.K <= 4096) q2_stage_row<F16, 1>(a, var, red, after_loads, tr);
+    else if (a.K <= 16384) q2_stage_row<F16, 4>(a, var, red, after_loads, tr);   // (all loads of x in flight at once)
     else q2_stage_row<F16, 0>(a, var, red, after_loads, tr);
     return;
   }
