@@ -530,7 +530,7 @@ def run_b200(a):
         ach = qbytes / gsec / 1e9      # in the step's own conditions: graph replay, dependent launch, back to back
         ach_eager = qbytes / qsec / 1e9
         traffic, traffic_src = ncu_traffic_per_launch(qbytes / nlaunch, a.bits)
-        line["roofline"] = {"bound": "hbm", "kernel": f"qmv_kernel<{a.bits}> + qmv2_kernel (TMA) on the wide matrices", "achieved": round(ach, 1), "peak": peak,
+        line["roofline"] = {"bound": "hbm", "kernel": ("qmv2_kernel (TMA-fed GEMV)" if a.bits == 4 and a.batch <= 8 else f"qmv_kernel<{a.bits}> / qmd_kernel"), "achieved": round(ach, 1), "peak": peak,
                             "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": traffic,
                             "traffic_source": traffic_src,
                             "launches_per_step": gl, "avg_launch_us": round(gsec / gl * 1e6, 2),
