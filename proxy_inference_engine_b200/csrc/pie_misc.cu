@@ -1,5 +1,7 @@
 // Small operators of the decode path: quantize / dequantize, RMSNorm, SwiGLU glue, residual add, arg-max.
 // Each cites the reference operator it stands in for (MLX = src/pie_core/external/mlx, PIE = src/proxy_inference_engine).
+#include <cstdlib>
+
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
 
@@ -180,10 +182,89 @@ __global__ void __launch_bounds__(1024) argmax_kernel(int32_t* out, const uint16
     }
   }
 }
+// The same over a thread-block cluster of 8 CTAs per row (one 1024-thread CTA reading 256 KB of logits is a 16 us chain
+// of L2 round trips at the end of every decode step): each CTA scans an eighth of the row with 16-byte loads, CTAs 1..7
+// push their candidate into CTA 0's shared memory (st.async counted by CTA 0's mbarrier), CTA 0 merges in index order
+// -- first maximum, as above -- and does the bookkeeping.  No global scratch, so concurrent calls cannot interfere.
+constexpr int kAmCluster = 8;
+__global__ void __launch_bounds__(1024) argmax_cluster_kernel(int32_t* out, const uint16_t* logits, int vocab,
+                                                              int32_t* pos_adv, int32_t* seq_out, int seq_ld) {
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  __shared__ __align__(8) uint32_t cand[kAmCluster][2];   // CTA 0: (value bits, index) of every part
+  __shared__ uint64_t bar;
+  const int part = blockIdx.x % kAmCluster, r = blockIdx.x / kAmCluster, tid = threadIdx.x;
+  if (part == 0 && tid == 0) {
+    mbar_init(&bar, 1);
+    mbar_arrive_expect_tx(&bar, (kAmCluster - 1) * 8);
+    fence_mbar_init();
+  }
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  const uint16_t* row = logits + (size_t)r * vocab;
+  const int per = ((vocab + kAmCluster - 1) / kAmCluster + 7) & ~7;   // multiple of 8 elements: 16-byte pieces
+  const int i0 = part * per, i1 = min(vocab, i0 + per);
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  auto take = [&](float v, int i) { if (v > best || (v == best && i < bi)) { best = v; bi = i; } };
+  if ((reinterpret_cast<uintptr_t>(row + i0) & 15) == 0) {
+    const int nv = i1 > i0 ? (i1 - i0) / 8 : 0;
+    for (int j = tid; j < nv; j += 1024) {
+      const uint4 q = ldcg128(row + i0 + 8 * j);
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { take(bf16lo(w[e]), i0 + 8 * j + 2 * e); take(bf16hi(w[e]), i0 + 8 * j + 2 * e + 1); }
+    }
+    for (int i = i0 + 8 * nv + tid; i < i1; i += 1024) take(bf16lo((uint32_t)row[i]), i);
+  } else {
+    for (int i = i0 + tid; i < i1; i += 1024) take(bf16lo((uint32_t)row[i]), i);
+  }
+  auto merge = [&](float ov, int oi) { if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; } };
+  for (int o = 16; o > 0; o >>= 1) merge(__shfl_xor_sync(0xffffffffu, best, o), __shfl_xor_sync(0xffffffffu, bi, o));
+  if ((tid & 31) == 0) { sv[tid >> 5] = best; si[tid >> 5] = bi; }
+  __syncthreads();
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // CTA 0's mbarrier is set up
+  if (tid < 32) {
+    best = sv[tid]; bi = si[tid];
+    for (int o = 16; o > 0; o >>= 1) merge(__shfl_xor_sync(0xffffffffu, best, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    if (tid == 0) {
+      if (part != 0) {
+        uint32_t ra, rb;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(&cand[part][0])), "r"(0));
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(smem_u32(&bar)), "r"(0));
+        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(ra),
+                     "r"(__float_as_uint(best)), "r"((uint32_t)bi), "r"(rb) : "memory");
+      } else {
+        mbar_wait(&bar, 0);
+        for (int p2 = 1; p2 < kAmCluster; ++p2) merge(__uint_as_float(cand[p2][0]), (int)cand[p2][1]);
+        const int tok = bi == 0x7fffffff ? 0 : bi;
+        out[r] = tok;
+        if (pos_adv) {  // the token just sampled occupies the next cache slot
+          const int np = pos_adv[r] + 1;
+          pos_adv[r] = np;
+          if (seq_out && np < seq_ld) seq_out[(size_t)r * seq_ld + np] = tok;
+        }
+      }
+    }
+  }
+}
+
 cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vocab, int32_t* pos_adv,
                           int32_t* seq_out, int seq_ld, cudaStream_t st) {
   if (rows == 0) return cudaSuccess;
   count_launch();
+  static const bool no_cluster = getenv("PIE_ARGMAX_CLUSTER") && atoi(getenv("PIE_ARGMAX_CLUSTER")) == 0;
+  if (!no_cluster && vocab >= 8192 && rows <= 64) {   // few long rows: the end of a decode step
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(rows * kAmCluster), 1, 1);
+    cfg.blockDim = dim3(1024, 1, 1);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kAmCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, argmax_cluster_kernel, out, logits, vocab, pos_adv, seq_out, seq_ld);
+  }
   argmax_kernel<<<rows, 1024, 0, st>>>(out, logits, vocab, pos_adv, seq_out, seq_ld);
   return cudaGetLastError();
 }

@@ -923,6 +923,8 @@ int pie_decode_step_plan(const pie_step_model* m, const pie_step_layer* layers, 
   return PIE_OK;
 }
 
+}  // extern "C"
+namespace pie {
 // sin / cos of the rotary angles of positions[b], once per step instead of once per layer and lane
 __global__ void rope_table_kernel(float* table, const int32_t* pos, const float* freqs, int half) {
   const int b = blockIdx.x;
@@ -934,6 +936,9 @@ __global__ void rope_table_kernel(float* table, const int32_t* pos, const float*
     table[(size_t)b * 2 * half + half + j] = cs;
   }
 }
+
+}  // namespace pie
+extern "C" {
 
 int pie_rope_table(float* table, const int32_t* positions, const float* freqs, int B, int half_dims, void* stream) {
   if (B == 0) return PIE_OK;

@@ -129,3 +129,25 @@ def test_decode_engine_samples_on_device_and_is_reproducible(env):
         row = logits[t]
         kth = np.sort(row)[-4]
         assert row[seq[t + 1]] >= kth - 0.05 * max(1.0, abs(kth)), (t, seq[t + 1])
+
+
+@pytest.mark.parametrize("rows,vocab", [(1, 128256), (3, 128256), (2, 8192), (5, 50001), (4, 640), (70, 9000)])
+def test_argmax_first_maximum_bookkeeping_and_cluster_form(env, rows, vocab):
+    """Greedy sampler (temp == 0, PIE/samplers/__init__.py:30-31 -> mx.argmax): first index of the row maximum, ties
+    included, for the one-CTA form (short / many rows) and the 8-CTA cluster form (few long rows: the decode step)."""
+    orc, ops, _ = env
+    rng = np.random.default_rng(rows * 1000 + vocab)
+    lg = orc.round_bf16(rng.standard_normal((rows, vocab)).astype(np.float32))
+    for r in range(rows):     # plant ties of the maximum, also across the boundaries of the cluster's parts
+        m = lg[r].max() + 1.0
+        idx = rng.choice(vocab, size=min(6, vocab), replace=False)
+        lg[r, idx] = m
+        if r == 0:
+            lg[r, [vocab - 1, vocab // 2]] = m
+    pos = torch.arange(rows, dtype=torch.int32, device="cuda")
+    seq = torch.zeros((rows, rows + 3), dtype=torch.int32, device="cuda")
+    got = ops.argmax(n2t_bf16(lg), positions_to_advance=pos, seq_out=seq).cpu().numpy()
+    ref = lg.argmax(-1)
+    assert (got == ref).all(), (got, ref)
+    assert pos.cpu().tolist() == [r + 1 for r in range(rows)]
+    assert [int(seq[r, r + 1]) for r in range(rows)] == ref.tolist()
