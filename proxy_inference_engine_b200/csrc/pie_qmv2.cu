@@ -53,7 +53,13 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int tid = threadIdx.x, lane = tid & 31;
-  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: TMA operands stay in uniform registers
+  // `warp` is the warp's SLOT in the CTA's run of units, not its hardware number: slots 4q .. 4q+3 are the four warps of
+  // scheduler q (hardware warp w issues on scheduler w % 4).  The run is cut into 16 consecutive shares of n or n + 1
+  // units; with slot == hardware warp the n + 1 shares of a x.5 split (q/k/v: 24 units, down: 56, gate/up: 104) all land on
+  // schedulers 1 and 3, and the main loop is issue-bound per scheduler: 8 / 16 / 28 units there against 6 / 14 / 26 when
+  // every scheduler gets two of each kind.  (PIE_QMV2_DBG & 64: slot = hardware warp.)
+  const int hw_warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: TMA operands stay in uniform registers
+  const int warp = (a.dbg & 64) ? hw_warp : (((hw_warp & 3) << 2) | (hw_warp >> 2));
   const int g = lane >> 2, t = lane & 3;
   constexpr int COLS = ONECOL ? 1 : 8;
 #define Q2_STAMP(i)                                                                        \
