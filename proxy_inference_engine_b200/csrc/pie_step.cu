@@ -176,7 +176,7 @@ __device__ __forceinline__ void rope_row(float* v, const float* sn, const float*
 // nsplit <= 8): their partials meet through distributed shared memory behind a cluster barrier instead of a global
 // workspace + fence + atomic + re-read, and every CTA of the cluster finishes a slice of the output.
 template <int D, int R, bool CLUSTER, int NW, bool PREWAIT = false>
-__device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag,
+__device__ __forceinline__ void attn_phase_impl(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag,
                                         unsigned long long* st = nullptr, uint64_t* cl_bar = nullptr) {
   constexpr int C = D / 64, E = 8 * C, PW = D + 2;
   auto stamp = [&](int i) { if (st && threadIdx.x == 0) st[i] = globaltimer_ns(); };
@@ -189,6 +189,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
     }
     asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // waited for just before the pushes
   }
+  stamp(8);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, tg = lane >> 3;
   const int units = s.B * s.Hkv * s.rg * s.nsplit;
   const int qkv_ld = (s.Hq + 2 * s.Hkv) * D;
@@ -209,6 +210,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
       s0 = __ldg(tb); s1 = __ldg(tb + 1); c0 = __ldg(tb + D / 8); c1 = __ldg(tb + D / 8 + 1);
     }
     const int p = s.pos[b], ctx = p + 1;
+    stamp(9 + (p < -5));
     const int per = (ctx + s.nsplit - 1) / s.nsplit;
     const int t0 = split * per, t1 = min(ctx, t0 + per);
     const size_t rec0 = ((size_t)b * s.Hq + qh0) * s.nsplit;
@@ -229,6 +231,7 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
       }
     };
     const int tb0 = t0 + warp * 4;
+    stamp(10);
     if (tb0 < t1) request_to(kn, vn, tb0, false);
     if (tb0 + NW * 4 < t1) request_to(kn2, vn2, tb0 + NW * 4, false);
     float sn[8], cs[8];
@@ -436,6 +439,15 @@ __device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, f
   }
 }
 
+// Out-of-line form for the one-launch step (four instantiations in one kernel).  The stand-alone launch inlines the body:
+// out of line, the __grid_constant__ parameter blocks are reached through generic pointers, and the chain
+// page table? -> strides -> cache pointers in front of the first K/V request cost ~0.8 us per launch (LD.E from the
+// parameter bank, three dependent round trips) where the inlined code reads constant-bank operands.
+template <int D, int R, bool CLUSTER, int NW>
+__device__ __noinline__ void attn_phase(const StepArgs& s, const StepPhase& P, float* scratch, int* s_flag) {
+  attn_phase_impl<D, R, CLUSTER, NW, false>(s, P, scratch, s_flag);
+}
+
 // a4: h[b, :] = dequantize(embed[tokens[b]]) -- same arithmetic as dequantize_kernel (pie_misc.cu): one packed word
 // per thread, w_hat = bf16(bf16(q * scale) + bias).
 __device__ __noinline__ void embed_phase(const StepArgs& s, int bits) {
@@ -505,7 +517,7 @@ __global__ void __launch_bounds__(kAttnWarps * 32, 1) attn_fused_kernel(const __
   __shared__ int s_flag;
   if (s.trace && threadIdx.x == 0) s.trace[blockIdx.x * 16] = globaltimer_ns();
   pdl_launch_dependents();
-  attn_phase<D, R, CLUSTER, kAttnWarps, true>(s, P, scratch, &s_flag, s.trace ? s.trace + blockIdx.x * 16 : nullptr, &cl_bar);
+  attn_phase_impl<D, R, CLUSTER, kAttnWarps, true>(s, P, scratch, &s_flag, s.trace ? s.trace + blockIdx.x * 16 : nullptr, &cl_bar);
   if (s.trace && threadIdx.x == 0) s.trace[blockIdx.x * 16 + 7] = globaltimer_ns();
 }
 
