@@ -357,14 +357,24 @@ __global__ void __launch_bounds__(kQ2Warps * 32, 1) qmv2_kernel(const __grid_con
   __syncthreads();
   Q2_STAMP_ORDERED(6)
   if (fin_tile >= 0) {
+    // slot (2 w + e) of the 32 parked shares lives in stage buffer (2 w + e); lane i looks at slot i, the ballot gives the
+    // slots of this tile (all of them at or before this warp's own), taken in slot (= k) order, four loads in flight
+    static_assert(kQ2Stages == 2 && kQ2Warps == 16, "one parked share per stage buffer, 32 slots");
+    unsigned m = __ballot_sync(0xffffffffu, edge_tile[lane] == fin_tile);
     float v[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int w2 = 0; w2 <= warp; ++w2) {
+    while (m) {
+      int sl[4];
 #pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        if (edge_tile[w2 * 2 + e] != fin_tile) continue;
-        const uint4 p = lds128(smem_s + (uint32_t)(w2 * kQ2Stages + e) * kQ2WBytes + lane * 16);
-        v[0] += __uint_as_float(p.x); v[1] += __uint_as_float(p.y);
-        v[2] += __uint_as_float(p.z); v[3] += __uint_as_float(p.w);
+      for (int i = 0; i < 4; ++i) { sl[i] = m ? __ffs(m) - 1 : -1; m &= m - 1; }
+      uint4 p[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        p[i] = sl[i] >= 0 ? lds128(smem_s + (uint32_t)sl[i] * kQ2WBytes + lane * 16) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (sl[i] < 0) break;   // (a parked -0.0f must not meet +0.0f padding: keep the sum exactly as the shares give it)
+        v[0] += __uint_as_float(p[i].x); v[1] += __uint_as_float(p[i].y);
+        v[2] += __uint_as_float(p[i].z); v[3] += __uint_as_float(p[i].w);
       }
     }
     epilogue(fin_tile, v);
