@@ -200,6 +200,15 @@ size_t pie_qmv_workspace_bytes(int M, long long n_total, int K, int bits, int du
     const size_t q = qmd_total_bytes(M, n_total, K, dual, bits);
     if (q > need) need = q;
   }
+  if (bits == 8 && K % 128 == 0) {   // pie_qmi.cu: planes + group sums + split-K partials behind the counter region
+    const int t0 = (int)((dual ? n_total : n_total) / 128);
+    size_t worst = 0;
+    for (int t = t0; t <= t0 + kMaxSeg; ++t) {
+      const size_t b = qmi_ws_bytes(t, K, qmi_pick_ksplit(t, K, dual));
+      if (b > worst) worst = b;
+    }
+    if (kWsCntBytes + worst > need) need = kWsCntBytes + worst;
+  }
   return need;
 }
 
@@ -241,6 +250,22 @@ int pie_qmv_fused_tp(void* out, int out_ld, const void* x, int x_ld, int M, int 
     // Batched-decode GEMM on tcgen05 (pie_qmd.cu).  PIE_QMD: 0 never, 1 where it measured faster than the GEMV at 32
     // rows (B200, 8B shapes, us GEMV / tcgen05: q8 gate+up 121 / 98, q8 head 417 / 290, q4 head 233 / 217; the narrow
     // matrices and 4-bit gate+up / down are still faster on the GEMV: DESIGN.md section 4.6), 2 wherever it is supported.
+    // 8-bit weights, more than 8 rows: the integer tensor cores take the packed weights as they are (pie_qmi.cu).
+    // PIE_QMI=0 keeps the bf16 forms below, 2 also routes 1..8 rows here.
+    const int qmi_mode = env_int("PIE_QMI", 1);
+    if (qmi_mode && (mb > 8 || qmi_mode == 2) && qmi_supported(mb, K, x_ld, group_size, bits, segs, nseg, a.dual)) {
+      int nt = 0;
+      for (int i = 0; i < nseg; ++i) nt += segs[i].N / 128;
+      if (a.dual) nt = segs[0].N / 128;
+      const int ks = qmi_pick_ksplit(nt, K, a.dual);
+      if (workspace && kWsCntBytes + qmi_ws_bytes(nt, K, ks) <= workspace_bytes && (size_t)nt * 32 <= kWsCntBytes) {
+        const int st2 = cuda_status(launch_qmi(a.out, out_ld, a.x, x_ld, mb, K, segs, nseg, norm_weight, eps, epilogue,
+                                               a.residual, ks, (uint8_t*)workspace + kWsCntBytes, (unsigned int*)workspace,
+                                               (cudaStream_t)stream));
+        if (st2 != PIE_OK) return st2;
+        continue;
+      }
+    }
     const int qmd_mode = env_int("PIE_QMD", 1);  // read per call: the tests switch it
     long long rows_total = 0;
     int nt = 0;

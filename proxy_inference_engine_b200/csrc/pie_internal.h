@@ -128,4 +128,12 @@ int build_qmv_args(QmvArgs& a, QmvPlan& p, void* out, int out_ld, const void* x,
                    int force_warps);
 int status_of(cudaError_t e);  // cudaError_t -> pie_status, recording the error string
 
+// int8-tensor-core batched-decode matmul for 8-bit weights (pie_qmi.cu)
+bool qmi_supported(int mb, int K, int x_ld, int group_size, int bits, const pie_qmv_seg* segs, int nseg, int dual);
+int qmi_pick_ksplit(int ntiles, int K, int dual);
+size_t qmi_ws_bytes(int ntiles, int K, int ksplit);
+cudaError_t launch_qmi(void* out, int out_ld, const void* x, int x_ld, int M, int K, const pie_qmv_seg* segs, int nseg,
+                       const void* norm_w, float eps, int epi, const void* residual, int ksplit, uint8_t* ws,
+                       unsigned int* ws_cnt, cudaStream_t st);
+
 }  // namespace pie

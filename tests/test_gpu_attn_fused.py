@@ -154,6 +154,7 @@ def test_batched_decode_gemm_tcgen05(env, bits, M, monkeypatch):
     for the narrow matrices, and M = 40 = one tcgen05 pass + one GEMV pass on the SAME workspace."""
     orc, ops = env
     monkeypatch.setenv("PIE_QMD", "2")  # everywhere it is supported (default: only where it measured faster)
+    monkeypatch.setenv("PIE_QMI", "0")  # (8-bit weights would otherwise go to the int8 kernel: tests/test_gpu_qmi.py)
     rng = np.random.default_rng(100 + bits + M)
     h, f, nq, nkv = 1024, 2048, 320, 128
     mk = lambda n, k: orc.quantize((rng.uniform(-1, 1, (n, k)) / np.sqrt(k)).astype(np.float32), 64, bits)

@@ -1,4 +1,3 @@
-python -m pytest tests/test_gpu_ops.py tests/test_gpu_model.py -x -q 2>&1 | tail -2
-python tools/timeline_step.py --layers 8 --dump gpurun_out/tl_m0.npy > gpurun_out/tl_m0.json 2>&1
-python bench.py --no-cpu-baseline --no-prefill --no-kernel-timing 2>/dev/null | cut -c1-130
-python bench.py --no-cpu-baseline --no-prefill --no-kernel-timing 2>/dev/null | cut -c1-130
+python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+python tools/bench_qmv.py --bits 8 --M 32 --graph 20 2>&1 | tail -1 | cut -c1-600
+python bench.py --bits 8 --batch 32 --prompt 2048 --paged --steps 32 --warmup 4 --no-cpu-baseline --no-kernel-timing --no-prefill 2>/dev/null | cut -c1-140
