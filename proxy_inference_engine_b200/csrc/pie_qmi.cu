@@ -33,7 +33,7 @@ namespace pie {
 constexpr int kQiRows = 128;     // weight rows per tile (MMA M)
 constexpr int kQiBK = 128;       // k per stage: one 128-byte swizzle atom, two quantization groups
 constexpr int kQiMb = 32;        // activation rows (MMA N = 2 planes x 32)
-constexpr int kQiStages = 6;
+constexpr int kQiStages = 6;     // (8 measured no faster: the stream is not depth-limited)
 constexpr int kQiABytes = kQiRows * kQiBK, kQiBBytes = 2 * kQiMb * kQiBK, kQiStageBytes = kQiABytes + kQiBBytes;
 constexpr int kQiAcc = 4;        // TMEM accumulator sets (one per stage in flight: 2 groups x 64 columns each)
 constexpr int kQiThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quadrant: 16 rows of the batch each)
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(kQiThreads, 1) qmi_kernel(const __grid_constan
               umma_i8(d, da + 4 * g, db + 4 * g, kQiIdesc, 0u);           // k 64 g .. 64 g + 31  (32-byte steps)
               umma_i8(d, da + 4 * g + 2, db + 4 * g + 2, kQiIdesc, 1u);
             }
-            umma_commit(&acc_full[buf]);   // one hand-over per stage: the commit -> wait -> release round trip is ~1 us
+            umma_commit(&acc_full[buf]);   // one hand-over per stage
           }
           ++gc;
           umma_commit(&empty[st]);

@@ -1,3 +1,5 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python tools/bench_qmv.py --bits 8 --M 32 --graph 20 2>&1 | tail -1 | cut -c1-600
-python bench.py --bits 8 --batch 32 --prompt 2048 --paged --steps 32 --warmup 4 --no-cpu-baseline --no-kernel-timing --no-prefill 2>/dev/null | cut -c1-140
+python -m pytest tests/test_gpu_qmi.py -x -q 2>&1 | tail -2
+for M in 1 4 8; do
+python tools/bench_qmv.py --bits 8 --M $M --graph 20 --pdl 1 2>&1 | tail -1 | cut -c1-500
+PIE_QMI=2 python tools/bench_qmv.py --bits 8 --M $M --graph 20 --pdl 1 2>&1 | tail -1 | cut -c1-500
+done
