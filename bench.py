@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
     ap.add_argument("--no-70b", action="store_true", help="N > 1: skip the Llama-3.1-70B tensor-parallel sub-records")
+    ap.add_argument("--no-config3", action="store_true", help="skip the 8-bit / batch-32 / paged-KV sub-record (BASELINE configs[2])")
     ap.add_argument("--no-prefill", action="store_true", help="skip the prefill GEMM figure (BASELINE config 4 shapes)")
     return ap.parse_args()
 
@@ -373,6 +374,35 @@ def tp_subrecord(model_name, bits, batches, rank, world, prompt=128, steps=32):
     return {"workload": f"{model_name} random-init MLX q{bits} gs64, tp{world}, prompt {prompt}", **out}
 
 
+def config3_subrecord(model_name, steps=24, warmup=4, batch=32, prompt=2048):
+    """BASELINE configs[2]: 8-bit weights, batch 32, paged KV cache, 2k context on one GPU -- the other end of the metric's
+    "bs 1/32".  Random-init model of its own (the headline model is 4-bit), device-timed like the headline value."""
+    import torch
+    from proxy_inference_engine_b200.checkpoint import build_model, preset_args, random_weights
+    from proxy_inference_engine_b200.decode import DecodeEngine
+    margs = preset_args(model_name, bits=8)
+    model = build_model(margs, random_weights(margs, seed=0, device="cuda"))
+    nums = model_numbers(margs, 8)
+    peak, _ = measured_peaks()
+    eng = DecodeEngine(model, batch=batch, max_context=prompt + steps + warmup + 40, paged=True)
+    ids = torch.randint(0, margs.vocab_size, (batch, prompt), generator=torch.Generator().manual_seed(1))
+    eng.prefill(ids)
+    eng.step(warmup)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); eng.step(steps); e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    step_bytes = nums["weight_bytes"] + batch * ((prompt + warmup + steps / 2) * nums["kv_bytes_per_ctx_token"])
+    out = {"workload": f"{model_name} random-init MLX q8 gs64, bs{batch} greedy decode, paged KV, prompt {prompt}",
+           "tok_s": round(batch / (ms * 1e-3), 1), "ms_per_step": round(ms, 3), "steps": steps, "warmup": warmup,
+           "bytes_per_step": int(step_bytes), "hbm_frac": round(step_bytes / (ms * 1e-3) / 1e9 / peak, 4),
+           "matmul_kernel": "qmi_kernel (tcgen05.mma kind::i8 over the packed 8-bit weights)"}
+    del eng, model
+    torch.cuda.empty_cache()
+    return out
+
+
 def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
     """dram__bytes_read.sum + dram__bytes_write.sum of the GEMV per launch, from the committed `ncu --set full` capture
     (profiles/r01e_prof_qmv_ncu_full_summary.csv: the q4 gate+up, down, qkv and o launches of one 8B layer).  The capture
@@ -542,6 +572,10 @@ def run_b200(a):
                                       "how": "CUDA-event pair around each launch in an eager pass (no graph / PDL)"}}
     if not a.no_prefill and world == 1:
         line["prefill_qmm"] = prefill_figure(margs, a.bits)
+    if not a.no_config3 and world == 1 and a.bits == 4 and a.batch == 1 and not a.layers:
+        del eng
+        torch.cuda.empty_cache()
+        line["config3_q8_bs32_paged_ctx2k"] = config3_subrecord(a.model)
     if not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(margs, a.bits)
     print(json.dumps(line), flush=True)
