@@ -410,7 +410,7 @@ def ncu_traffic_per_launch(alg_bytes_per_launch, bits):
     average launch.  None if the capture is absent or was taken at another bit width."""
     import csv
     pdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles")
-    path = os.path.join(pdir, "r02b_prof_qmv_ncu_full_summary.csv")   # this round's capture (both GEMV kernels)
+    path = os.path.join(pdir, "r02c_prof_qmv_ncu_full_summary.csv")   # this round's capture (both GEMV kernels)
     if not os.path.exists(path):
         path = os.path.join(pdir, "r01e_prof_qmv_ncu_full_summary.csv")
     if bits != 4 or not os.path.exists(path):
