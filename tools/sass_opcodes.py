@@ -1,12 +1,12 @@
 """Opcode histogram of every kernel in libpie_b200.so (cuobjdump -sass): which kernels carry TMA (UTMALDG), tcgen05
-(UTCHMMA / UTCBAR / LDTM), mbarrier (SYNCS), legacy tensor-core (HMMA) and cluster (UCGABAR, ST.ASYNC) instructions.
+(UTCHMMA = bf16, UTCIMMA = int8, UTCBAR, LDTM), mbarrier (SYNCS), legacy tensor-core (HMMA) and cluster (UCGABAR, ST.ASYNC) instructions.
    python tools/sass_opcodes.py > profiles/sass_opcodes_r02.txt"""
 import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 so = os.path.join(ROOT, "proxy_inference_engine_b200", "libpie_b200.so")
 out = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
 demangle = lambda n: subprocess.run(["cu++filt", n], capture_output=True, text=True).stdout.strip() or n
-MARK = ["UTMALDG", "UTMAPF", "UTMACCTL", "UTCHMMA", "UTCQMMA", "UTCBAR", "UTCCP", "LDTM", "STTM", "SYNCS", "HMMA", "IMMA", "UCGABAR",
+MARK = ["UTMALDG", "UBLKCP", "UTMAPF", "UTMACCTL", "UTCHMMA", "UTCIMMA", "UTCQMMA", "UTCBAR", "UTCCP", "LDTM", "STTM", "SYNCS", "HMMA", "IMMA", "UCGABAR",
         "STAS", "ST.ASYNC", "LDGSTS", "ACQBULK", "PREEXIT", "ELECT", "MUFU", "LOP3", "FFMA", "LDS", "LDG", "STG", "BAR"]
 kern, cur = collections.OrderedDict(), None
 for line in out.splitlines():
