@@ -513,11 +513,9 @@ cudaError_t launch_qmi(void* out, int out_ld, const void* x, int x_ld, int M, in
   a.ws_part = (float*)((uint8_t*)gsum + ((((size_t)(K / kGroup) * kQiMb * 4) + 255) & ~(size_t)255));
   a.ws_cnt = ws_cnt;
   if (!qi_map(&a.xmap, xq, 2 * kQiMb, K, 2 * kQiMb)) return cudaErrorInvalidValue;
-  static bool configured = false;
-  if (!configured) {
+  {  // (per launch, not once per process: the attribute is per device)
     cudaError_t e = cudaFuncSetAttribute(qmi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kQiSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   count_launch();
   qmi_prep_kernel<<<kQiMb, 1024, 0, st>>>(xq, rscale, gsum, (const uint16_t*)x, x_ld, (const uint16_t*)norm_w, eps, M, K);
