@@ -288,6 +288,36 @@ int pie_decode_step_plan(const pie_step_model* model, const pie_step_layer* laye
                          void* plan_host, size_t plan_bytes);
 int pie_decode_step(const void* plan_dev, const void* plan_host, size_t plan_bytes, void* sync_ws, void* stream);
 
+/* ---- f2  paged-KV page allocator: fixed pool of 64-token pages, reference counts, lock-free LIFO free list ------
+ * (PageAllocator, CORE/include/engine/page_allocator.hpp:17-72, CORE/src/engine/page_allocator.cpp:8-158; KVPage's
+ *  counters, CORE/include/engine/page.hpp:84-123; tests CORE-level tests/cpp/test_page_allocator.cpp).
+ * Host-side: a page id indexes the pool tensors of cache.PagedKVCache in HBM and goes into the page tables the attention
+ * kernels read (pie_kv_layout.page_table).  create returns NULL for num_pages == 0, num_heads <= 0 or head_dim <= 0
+ * (std::invalid_argument in the reference); allocate returns -1 when the pool is exhausted (std::nullopt); free / add_ref
+ * return PIE_EINVAL_SHAPE for an id outside the pool (std::out_of_range).  All calls are thread-safe and lock-free;
+ * pools of up to 2^24 - 2 pages (the free count and the list head share one 64-bit word).                          */
+#define PIE_PAGE_TOKENS 64
+typedef struct pie_page_allocator pie_page_allocator;
+pie_page_allocator* pie_page_allocator_create(size_t num_pages, int num_heads, int head_dim);
+void pie_page_allocator_destroy(pie_page_allocator* a);
+long long pie_page_allocate(pie_page_allocator* a);                 /* allocate_page(): ref count 1, num_tokens 0 */
+int pie_page_free(pie_page_allocator* a, uint32_t page_id);         /* free_page(): back on the free list at count 0 */
+int pie_page_add_ref(pie_page_allocator* a, uint32_t page_id);      /* add_ref(): sharing (prefix reuse) */
+long long pie_page_ref_count(const pie_page_allocator* a, uint32_t page_id);   /* -1: id outside the pool */
+long long pie_page_num_tokens(const pie_page_allocator* a, uint32_t page_id);
+int pie_page_set_num_tokens(pie_page_allocator* a, uint32_t page_id, uint32_t n);
+size_t pie_page_allocator_size(const pie_page_allocator* a);
+size_t pie_page_allocator_num_free(const pie_page_allocator* a);    /* get_num_free_pages() */
+/* whole sequences at a time (no reference counterpart): n pages, all or nothing (PIE_EWORKSPACE when the pool is short) */
+int pie_page_allocate_n(pie_page_allocator* a, int32_t* out_ids, int n);
+int pie_page_free_n(pie_page_allocator* a, const int32_t* ids, int n);
+int pie_page_add_ref_n(pie_page_allocator* a, const int32_t* ids, int n);
+/* the reference's own scenario benchmark and contention test, run natively on this allocator:
+ * BM_PageAllocator_ReferenceCountingScenario (benchmarks/cpp/core/page_allocator_benchmark.cpp:191-300) -> ms per
+ * iteration; HighContentionPushPopStress (tests/cpp/test_page_allocator.cpp:278-330) -> pages lost or handed out twice */
+double pie_page_allocator_bench_refcount(pie_page_allocator* a, int iterations);
+long long pie_page_allocator_stress(pie_page_allocator* a, int threads, int ops_per_thread);
+
 /* Profiling aid (no reference counterpart): after this call every TMA GEMV and fused-attention launch writes up to
  * sixteen %globaltimer stamps per CTA (entry, first loads issued, dependency wait returned, activations staged, first
  * weights landed, main loop done, CTA reduction, exit, ...) into the next 32 KB slot of `buf` (device memory).  NULL

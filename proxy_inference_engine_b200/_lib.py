@@ -99,6 +99,21 @@ SIGNATURES = {
     "pie_tp_gather_offset": (_sz, [_i, _i]),
     "pie_tp_allreduce": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(TpPeers), _vp]),
     "pie_tp_allgather": (_i, [_vp, _i, _i, C.POINTER(TpPeers), _vp]),
+    "pie_page_allocator_create": (_vp, [_sz, _i, _i]),
+    "pie_page_allocator_destroy": (None, [_vp]),
+    "pie_page_allocate": (_ll, [_vp]),
+    "pie_page_free": (_i, [_vp, C.c_uint32]),
+    "pie_page_add_ref": (_i, [_vp, C.c_uint32]),
+    "pie_page_ref_count": (_ll, [_vp, C.c_uint32]),
+    "pie_page_num_tokens": (_ll, [_vp, C.c_uint32]),
+    "pie_page_set_num_tokens": (_i, [_vp, C.c_uint32, C.c_uint32]),
+    "pie_page_allocator_size": (_sz, [_vp]),
+    "pie_page_allocator_num_free": (_sz, [_vp]),
+    "pie_page_allocate_n": (_i, [_vp, _vp, _i]),
+    "pie_page_free_n": (_i, [_vp, _vp, _i]),
+    "pie_page_add_ref_n": (_i, [_vp, _vp, _i]),
+    "pie_page_allocator_bench_refcount": (C.c_double, [_vp, _i]),
+    "pie_page_allocator_stress": (_ll, [_vp, _i, _i]),
     "pie_debug_stamps": (_i, [_vp, _sz]),
     "pie_sample": (_i, [_vp, _vp, _i, _i, _i, _f, _f, _f, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "pie_decode_step_plan_bytes": (_sz, [_i]),

@@ -112,9 +112,18 @@ class DecodeEngine:
         # caches
         self.paged = paged
         if paged:
+            # Pages come from the pool's allocator (paging.PageAllocator over csrc/pie_pages.cu: reference counts, LIFO free
+            # list).  To keep the page tables as scattered as a long-running server's, the pool is first drained and handed
+            # back in a seeded random order; every row then takes the pages of its whole context.
+            from .paging import PageAllocator
             n_pg = (max_context + 63) // 64
+            self.page_allocator = PageAllocator(B * n_pg, self.Hkv, self.D)
             g = torch.Generator(device="cpu").manual_seed(seed)
-            perm = torch.randperm(B * n_pg, generator=g).to(torch.int32).reshape(B, n_pg).to(dev)
+            order = torch.randperm(B * n_pg, generator=g).tolist()
+            self.page_allocator.allocate_pages(B * n_pg)
+            self.page_allocator.free_pages(order)
+            rows = [self.page_allocator.allocate_pages(n_pg) for _ in range(B)]
+            perm = torch.tensor(rows, dtype=torch.int32).to(dev)
             self.page_table = perm
             self.cache = [PagedKVCache(torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev),
                                        torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev), perm)

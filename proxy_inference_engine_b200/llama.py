@@ -84,8 +84,12 @@ def scaled_dot_product_attention(queries, keys, values, cache, scale, mask):
     if isinstance(keys, PagedKVCache):
         c = keys
         B, Hq, L, D = queries.shape
-        if L != 1 or mask is not None:
-            raise ValueError("PagedKVCache serves decode steps (L == 1); prefill goes through KVCache")
+        if L > 1:   # prefill (also a continuation behind re-used prefix pages): the kernel walks the page table
+            if not isinstance(mask, ops.CausalMask) or mask.L != L or mask.offset + L != c.offset:
+                raise ValueError("PagedKVCache prefill needs the causal mask of create_attention_mask")
+            return ops.prefill_attention(queries, c.k_pool, c.v_pool, c.layout(), mask.offset, scale)
+        if mask is not None:
+            raise ValueError("PagedKVCache decode step takes no mask")
         pos = torch.full((B,), c.offset - 1, dtype=torch.int32, device=queries.device)
         out = ops.decode_attention(queries.reshape(B, Hq, D).contiguous(), c.k_pool, c.v_pool, c.layout(), pos, scale,
                                    max_context=c.offset)

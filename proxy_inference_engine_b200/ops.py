@@ -282,6 +282,17 @@ def scaled_dot_product_attention(q, k, v, *, scale: float, mask=None):
     return out.view(B, Lq, Hq, D).permute(0, 2, 1, 3)
 
 
+def prefill_attention(q, kbuf, vbuf, lay: KvLayout, offset: int, scale: float):
+    """Causal attention of L > 1 new tokens over a cache that already holds them (T = offset + L) on explicit cache
+    geometry, contiguous or paged: chunked prefill / prefix reuse.  q [B, Hq, L, D] -> [B, Hq, L, D]."""
+    B, Hq, Lq, D = q.shape
+    Hkv = kbuf.shape[1] if lay.page_table is None else kbuf.shape[2]
+    out = torch.empty((B, Lq, Hq * D), dtype=_BF16, device=q.device)
+    _lib.check(_lib.load().pie_prefill_attn(_p(out), _p(q.contiguous()), _p(kbuf), _p(vbuf), C.byref(lay), B, Hq, Hkv, Lq, D,
+                                            int(offset), float(scale), _stream()), "scaled_dot_product_attention")
+    return out.view(B, Lq, Hq, D).permute(0, 2, 1, 3)
+
+
 def silu_mul(gate, up):
     """nn.silu(gate) * up with a bf16 rounding at each MLX op boundary (language.py:126-127)."""
     gate, up = gate.contiguous(), up.contiguous()
