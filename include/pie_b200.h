@@ -175,6 +175,37 @@ int pie_prefill_attn(void* out, const void* q, const void* kcache, const void* v
                      const pie_kv_layout* kv_host, int B, int Hq, int Hkv, int L, int D, int offset, float scale,
                      void* stream);
 
+/* ---- (f3) quantised KV cache: QuantizedKVCache.update_and_fetch (PIE/cache/kv_cache/quantized.py:38-108) and
+ * quantized_scaled_dot_product_attention for L == 1 (PIE/models/base.py:56-89), 8 bits, groups of 64 along head_dim.
+ * The cache is the reference's state tuple per K and V: quants u32 [slots, D / 4] (byte e of a row = element e, the
+ * packing of mx.quantize), scales and biases bf16 [slots, D / 64]; slot of (row b, kv head h, token t) =
+ * (b * Hkv + h) * capacity + t, or with a page table (page_table[b * pt_stride + t / page_size] * Hkv + h) * page_size
+ * + t % page_size.  The struct lives on the host and is read at the call.
+ *   pie_kvq_append : pie_rope_kv_append with a quantised cache -- q heads rotated into q_out, k heads rotated, rounded
+ *                    to bf16 and quantised into the cache at positions[b], v heads quantised into the cache;
+ *                    bit-exact with mx.quantize of the bf16 rows.
+ *   pie_kvq_write  : pie_kv_write with a quantised cache (prefill; k already rotated).
+ *   pie_decode_attn_q8 : pie_decode_attn over the quantised cache; K, V and the scores are never materialised
+ *                    (q.k = s * sum(q kq) + b * sum(q) per group), fp32 throughout, one bf16 rounding at the store.
+ *                    Workspace and its zero-at-allocation contract as pie_decode_attn; nsplit from
+ *                    pie_decode_attn_q8_pick_splits.                                                              */
+typedef struct pie_kvq_cache {
+  uint32_t* k_quant; void* k_scales; void* k_biases;
+  uint32_t* v_quant; void* v_scales; void* v_biases;
+  long long capacity;          /* tokens per (row, kv head), even; unused with a page table (page_size: a power of two) */
+  const int32_t* page_table;   /* device int32 [B, pt_stride] or NULL */
+  int pt_stride, page_size;
+  int group_size, bits;        /* 64, 8 */
+} pie_kvq_cache;
+int pie_kvq_append(void* q_out, const void* qkv, const pie_kvq_cache* cache_host, const int32_t* positions,
+                   const float* freqs, int B, int Hq, int Hkv, int D, void* stream);
+int pie_kvq_write(const pie_kvq_cache* cache_host, const void* k, const void* v, int B, int Hkv, int L, int D,
+                  int offset, void* stream);
+int pie_decode_attn_q8_pick_splits(int B, int Hq, int Hkv, int max_context);
+int pie_decode_attn_q8(void* out, const void* q, const pie_kvq_cache* cache_host, const int32_t* positions, int B,
+                       int Hq, int Hkv, int D, float scale, int nsplit, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
 /* ---- a11 glue: nn.silu(g) * u and h + r, bf16 with a rounding at each MLX op boundary ------------------ */
 int pie_silu_mul(void* out, const void* gate, const void* up, long long n, void* stream);
 int pie_add(void* out, const void* a, const void* b, long long n, void* stream);

@@ -92,6 +92,8 @@ def ref():
         R.pie_ref_qmm_t_bf16.argtypes = [_u16p, _u16p, _u32p, _u16p, _u16p] + [C.c_int] * 5
         R.pie_ref_qmm_t_f32_mt.argtypes = [_f32p, _f32p, _u32p, _f32p, _f32p] + [C.c_int] * 6
         R.pie_ref_qmm_t_bf16_mt.argtypes = [_u16p, _u16p, _u32p, _u16p, _u16p] + [C.c_int] * 6
+        R.pie_ref_qmm_n_f32.argtypes = [_f32p, _f32p, _u32p, _f32p, _f32p] + [C.c_int] * 5
+        R.pie_ref_qmm_n_bf16.argtypes = [_u16p, _u16p, _u32p, _u16p, _u16p] + [C.c_int] * 5
         R.pie_ref_simd_max_size_f32.restype = C.c_int
         R.pie_ref_max_threads.restype = C.c_int
         _ref = R
@@ -194,13 +196,13 @@ def dequantize(wq, scales, biases, group_size: int = 64, bits: int = 4, ids=None
 
 def quantized_matmul(x, wq, scales, biases, transpose: bool = True, group_size: int = 64,
                      bits: int = 4, mode: str = "B", sequential: bool = False) -> np.ndarray:
-    """mx.quantized_matmul(transpose=True) (MLX/mlx/ops.cpp:3984-4021; checks :74-137).
+    """mx.quantized_matmul (MLX/mlx/ops.cpp:3984-4021; checks :74-137); transpose=False -> _quantized_matmul_n.
 
     mode 'A': float32 result; 'B': result rounded to bf16; 'T': reference-exact bf16 scalar path
     (`_qmm_t<bfloat16_t>`, every op rounded).  sequential=True uses the strict k-order of `_qmm_t`.
     """
     if not transpose:
-        raise ValueError("oracle restates transpose=True only (the QuantizedLinear path)")
+        return _quantized_matmul_n(x, wq, scales, biases, group_size, bits, mode)
     wq = np.ascontiguousarray(wq, dtype=np.uint32)
     x, scales, biases = f32(x), f32(scales), f32(biases)
     if scales.shape != biases.shape:
@@ -225,6 +227,73 @@ def quantized_matmul(x, wq, scales, biases, transpose: bool = True, group_size: 
     else:
         lib().orc_qmm_t(*args, 1 if mode == "B" else 0)
     return y.reshape(x.shape[:-1] + (N,))
+
+
+def _quantized_matmul_n(x, wq, scales, biases, group_size, bits, mode) -> np.ndarray:
+    """transpose=False: y[m, n] = sum_k x[m, k] * (scales[k, n/gs] * q[k, n] + biases[k, n/gs]), w quantised along N
+    (`_qmm`, MLX/mlx/backend/cpu/quantized.cpp:38-94: k outer, `result[n] += xi * (scale * w + bias)`).  Leading batch
+    dimensions of x and w broadcast as in MLX.  mode 'A': float32 in the reference's order; 'B': that, rounded to bf16;
+    'T': `_qmm<bfloat16_t>` -- every operation rounded to bf16."""
+    wq = np.ascontiguousarray(wq, dtype=np.uint32)
+    x, scales, biases = f32(x), f32(scales), f32(biases)
+    if scales.shape != biases.shape:
+        raise ValueError("[quantized_matmul] Scales and biases should have the same shape.")
+    N = wq.shape[-1] * 32 // bits
+    if N != scales.shape[-1] * group_size:
+        raise ValueError("[quantized_matmul] The shapes of the weight and scales are incompatible "
+                         "based on bits and group_size.")
+    K = wq.shape[-2]
+    if x.shape[-1] != K:
+        raise ValueError(f"[quantized_matmul] Last dimension of first input with shape {x.shape} "
+                         f"does not match the expanded quantized matrix ({K}, {N})")
+    q = unpack(wq, bits).astype(np.float32)                               # [..., K, N]
+    s = np.repeat(scales, group_size, axis=-1)
+    b = np.repeat(biases, group_size, axis=-1)
+    r = round_bf16 if mode == "T" else (lambda a: a)
+    wf = r(r(s * q) + b)                                                   # scale * w + bias
+    y = np.zeros(np.broadcast_shapes(x.shape[:-2], wf.shape[:-2]) + (x.shape[-2], N), np.float32)
+    for k in range(K):
+        y = r(y + r(x[..., :, k, None] * wf[..., None, k, :]))
+    return round_bf16(y) if mode == "B" else y
+
+
+def softmax(x, mode: str = "B") -> np.ndarray:
+    """mx.softmax(axis=-1) (MLX/mlx/backend/cpu/softmax.cpp): max, exp(x - max), sum, divide, in float32."""
+    x = f32(x)
+    e = np.exp(x - x.max(axis=-1, keepdims=True), dtype=np.float32)
+    y = e / e.sum(axis=-1, keepdims=True, dtype=np.float32)
+    return round_bf16(y) if mode != "A" else y
+
+
+def quantized_scaled_dot_product_attention(queries, q_keys, q_values, scale: float, mask=None, group_size: int = 64,
+                                           bits: int = 8, mode: str = "B") -> np.ndarray:
+    """PIE/models/base.py:56-89.  queries [B, Hq, L, D]; q_keys / q_values = (quants, scales, biases) [B, Hkv, T, .].
+    mode 'A': float32 with no intermediate rounding; 'B': bf16 rounding at every MLX op boundary (queries * scale,
+    scores, + mask, softmax, out) with float32 inside the matmuls; 'T': additionally the matmuls are the x86 scalar
+    bf16 kernels (`_qmm_t` / `_qmm`, every operation rounded) -- what the reference computes on this CPU."""
+    queries = f32(queries)
+    B, Hq, L, D = queries.shape
+    Hkv = q_keys[0].shape[-3]
+    n_rep = Hq // Hkv
+    r = (lambda a: a) if mode == "A" else round_bf16
+    mm = "A" if mode == "A" else mode
+    queries = r(queries * np.float32(scale))
+    if n_rep > 1:
+        queries = queries.reshape(B, Hkv, n_rep, L, D)
+    out = np.empty((B, Hkv, n_rep, L, q_values[0].shape[-1] * 32 // bits), np.float32)
+    for b_ in range(B):
+        for h in range(Hkv):
+            qk = tuple(np.asarray(t)[b_, h] for t in q_keys)
+            qv = tuple(np.asarray(t)[b_, h] for t in q_values)
+            x = queries[b_, h].reshape(n_rep * L, D) if n_rep > 1 else queries[b_, h]
+            sc = quantized_matmul(x, *qk, transpose=True, group_size=group_size, bits=bits, mode=mm,
+                                  sequential=(mode == "T"))
+            if mask is not None:
+                sc = r(sc.reshape(n_rep, L, -1) + f32(mask)).reshape(n_rep * L, -1)
+            sc = softmax(sc, mode)
+            out[b_, h] = quantized_matmul(sc, *qv, transpose=False, group_size=group_size, bits=bits,
+                                          mode=mm).reshape(n_rep, L, -1)
+    return out.reshape(B, Hq, L, -1)
 
 
 def rms_norm(x, weight, eps: float, mode: str = "B") -> np.ndarray:
@@ -415,6 +484,43 @@ class KVCache:
         return self.keys[:, :, :self.offset], self.values[:, :, :self.offset]
 
 
+class QuantizedKVCache:
+    """QuantizedKVCache (PIE/cache/kv_cache/quantized.py:8-108): (quants, scales, biases) triples, capacity in steps
+    of 256, mx.quantize of the new rows (bf16 tensors)."""
+
+    def __init__(self, group_size: int = 64, bits: int = 8, step: int = 256):
+        self.keys = None
+        self.values = None
+        self.offset = 0
+        self.step = step
+        self.group_size = group_size
+        self.bits = bits
+
+    def update_and_fetch(self, k, v):
+        B, H, n, D = k.shape
+        prev = self.offset
+        if self.keys is None or prev + n > self.keys[0].shape[2]:
+            new_steps = (self.step + n - 1) // self.step * self.step
+            cap = (prev if self.keys is not None else 0) + new_steps
+
+            def init(dim, old):
+                t = (np.zeros((B, H, cap, dim * self.bits // 32), np.uint32),
+                     np.zeros((B, H, cap, dim // self.group_size), np.float32),
+                     np.zeros((B, H, cap, dim // self.group_size), np.float32))
+                if old is not None:
+                    for a, o in zip(t, old):
+                        a[:, :, :prev] = o[:, :, :prev]
+                return t
+            self.keys, self.values = init(D, self.keys), init(v.shape[-1], self.values)
+        self.offset += n
+        for dst, src in zip(self.keys, quantize(k, self.group_size, self.bits)):
+            dst[:, :, prev:self.offset] = src
+        for dst, src in zip(self.values, quantize(v, self.group_size, self.bits)):
+            dst[:, :, prev:self.offset] = src
+        cut = lambda t: t[:, :, :self.offset]
+        return tuple(map(cut, self.keys)), tuple(map(cut, self.values))
+
+
 class LlamaOracle:
     """Model.__call__ (PIE/models/llama/language.py:199-210) over MLX-layout quantized weights.
 
@@ -441,7 +547,9 @@ class LlamaOracle:
                                   float(rs.get("high_freq_factor", 1.0)), max_len, max_len)
         self.layers = list(range(args.num_hidden_layers))
 
-    def make_cache(self):
+    def make_cache(self, kv_bits=None, kv_group_size: int = 64):
+        if kv_bits is not None:
+            return [QuantizedKVCache(kv_group_size, kv_bits) for _ in self.layers]
         return [KVCache() for _ in self.layers]
 
     def _linear(self, x, prefix):
@@ -479,8 +587,11 @@ class LlamaOracle:
             k = rope(k, self.head_dim, a.rope_traditional, None, 1.0, off, self.freqs, m)
             if c is not None:
                 k, v = c.update_and_fetch(k, v)
-            o = scaled_dot_product_attention(q, np.ascontiguousarray(k), np.ascontiguousarray(v),
-                                             self.scale, mask, -1, m)
+            if isinstance(c, QuantizedKVCache):   # base.py:101-110
+                o = quantized_scaled_dot_product_attention(q, k, v, self.scale, mask, c.group_size, c.bits, m)
+            else:
+                o = scaled_dot_product_attention(q, np.ascontiguousarray(k), np.ascontiguousarray(v),
+                                                 self.scale, mask, -1, m)
             o = o.transpose(0, 2, 1, 3).reshape(B, L, -1)
             r = self._linear(o, p + ".self_attn.o_proj")
             h = add(h, r, m)

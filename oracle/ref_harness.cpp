@@ -6,6 +6,8 @@
 //   quantize<T,U>            MLX/mlx/backend/cpu/quantized.cpp:603-661
 //   _qmm_t<T,bits,gs>        MLX/mlx/backend/cpu/quantized.cpp:96-153   (the x86 path: simd::max_size==1,
 //                            MLX/mlx/backend/cpu/simd/base_simd.h:13-14 -> dispatch at quantized.cpp:240-244)
+//   _qmm<T,bits,gs>          MLX/mlx/backend/cpu/quantized.cpp:38-94    (transpose=False: the values product of
+//                            quantized_scaled_dot_product_attention, PIE/models/base.py:81-83)
 // (MLX = /root/reference/src/pie_core/external/mlx).  Built by oracle/Makefile into
 // oracle/_ref/libpie_ref.so (git-ignored, NOT gpurun-ignored).  Unreferenced eval_cpu bodies that need
 // libmlx symbols are discarded with -ffunction-sections/--gc-sections.
@@ -34,6 +36,16 @@ void qmm_t_dispatch(T* y, const T* x, const uint32_t* w, const T* s, const T* b,
   if (bits == B && gs == G) { _qmm_t<T, B, G>(y, x, w, s, b, M, N, K); return; }
   PIE_CASE(4, 64) PIE_CASE(8, 64) PIE_CASE(4, 32) PIE_CASE(8, 32) PIE_CASE(4, 128) PIE_CASE(8, 128)
   PIE_CASE(2, 64) PIE_CASE(2, 32) PIE_CASE(2, 128)
+#undef PIE_CASE
+}
+
+template <typename T>
+void qmm_n_dispatch(T* y, const T* x, const uint32_t* w, const T* s, const T* b,
+                    int M, int N, int K, int bits, int gs) {
+  using namespace mlx::core;
+#define PIE_CASE(B, G) \
+  if (bits == B && gs == G) { _qmm<T, B, G>(y, x, w, s, b, M, N, K); return; }
+  PIE_CASE(4, 64) PIE_CASE(8, 64) PIE_CASE(4, 32) PIE_CASE(8, 32) PIE_CASE(4, 128) PIE_CASE(8, 128)
 #undef PIE_CASE
 }
 
@@ -108,6 +120,19 @@ void pie_ref_qmm_t_bf16_mt(uint16_t* y, const uint16_t* x, const uint32_t* w, co
       reinterpret_cast<bfloat16_t*>(y), reinterpret_cast<const bfloat16_t*>(x), w,
       reinterpret_cast<const bfloat16_t*>(s), reinterpret_cast<const bfloat16_t*>(b), M, N, K, bits,
       group_size, nthreads);
+}
+
+// ---- _qmm<T,bits,gs>  (quantized.cpp:38-94): y [M, N] = x [M, K] @ dequant(w [K, N]) -------------------
+void pie_ref_qmm_n_f32(float* y, const float* x, const uint32_t* w, const float* s, const float* b,
+                       int M, int N, int K, int bits, int group_size) {
+  qmm_n_dispatch<float>(y, x, w, s, b, M, N, K, bits, group_size);
+}
+void pie_ref_qmm_n_bf16(uint16_t* y, const uint16_t* x, const uint32_t* w, const uint16_t* s,
+                        const uint16_t* b, int M, int N, int K, int bits, int group_size) {
+  qmm_n_dispatch<bfloat16_t>(
+      reinterpret_cast<bfloat16_t*>(y), reinterpret_cast<const bfloat16_t*>(x), w,
+      reinterpret_cast<const bfloat16_t*>(s), reinterpret_cast<const bfloat16_t*>(b), M, N, K, bits,
+      group_size);
 }
 
 int pie_ref_max_threads() {

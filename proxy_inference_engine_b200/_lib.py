@@ -29,6 +29,14 @@ class KvLayout(C.Structure):
                 ("page_table", C.c_void_p), ("pt_stride", C.c_int), ("page_size", C.c_int)]
 
 
+class KvqCache(C.Structure):
+    """pie_kvq_cache"""
+    _fields_ = [("k_quant", C.c_void_p), ("k_scales", C.c_void_p), ("k_biases", C.c_void_p),
+                ("v_quant", C.c_void_p), ("v_scales", C.c_void_p), ("v_biases", C.c_void_p),
+                ("capacity", C.c_longlong), ("page_table", C.c_void_p), ("pt_stride", C.c_int), ("page_size", C.c_int),
+                ("group_size", C.c_int), ("bits", C.c_int)]
+
+
 class TpPeers(C.Structure):
     """pie_tp_peers"""
     _fields_ = [("base", C.c_void_p * 8), ("rank", C.c_int), ("world", C.c_int), ("max_elems", C.c_int),
@@ -86,6 +94,10 @@ SIGNATURES = {
     "pie_decode_attn_pick_splits": (_i, [_i, _i, _i, _i]),
     "pie_decode_attn": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
     "pie_rope_table": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "pie_kvq_append": (_i, [_vp, _vp, C.POINTER(KvqCache), _vp, _vp, _i, _i, _i, _i, _vp]),
+    "pie_kvq_write": (_i, [C.POINTER(KvqCache), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "pie_decode_attn_q8_pick_splits": (_i, [_i, _i, _i, _i]),
+    "pie_decode_attn_q8": (_i, [_vp, _vp, C.POINTER(KvqCache), _vp, _i, _i, _i, _i, _f, _i, _vp, _sz, _vp]),
     "pie_decode_attn_static": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _i, _i, _i, _i, _f, _i, _vp]),
     "pie_decode_attn_fused": (_i, [_vp, _vp, _vp, _vp, C.POINTER(KvLayout), _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _vp,
                                    _sz, _i, _vp]),

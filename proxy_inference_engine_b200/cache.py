@@ -97,3 +97,102 @@ class PagedKVCache:
         k = self.k_pool[pages, slot]  # [B, T, H, D]
         v = self.v_pool[pages, slot]
         return k.permute(0, 2, 1, 3).contiguous(), v.permute(0, 2, 1, 3).contiguous()
+
+
+class QuantizedKVCache:
+    """QuantizedKVCache (PIE/cache/kv_cache/quantized.py:8-140): keys / values are (quants uint32 [B, n_kv, cap, D*bits/32],
+    scales, biases bf16 [B, n_kv, cap, D/group_size]) triples growing in steps of 256 tokens; ``update_and_fetch``
+    quantises the new rows with mx.quantize's arithmetic (pie_kvq_write, bit-exact) and returns the triples cut to
+    ``offset``.  8 bits, groups of 64 are built here; anything else raises as an unsupported configuration."""
+    step = 256
+
+    def __init__(self, group_size: int = 64, bits: int = 8, capacity: int = 0):
+        if group_size != 64 or bits != 8:
+            raise ValueError(f"QuantizedKVCache: group_size={group_size}, bits={bits} not built here (64, 8)")
+        self.keys = None
+        self.values = None
+        self.offset = 0
+        self.group_size = group_size
+        self.bits = bits
+        self._reserve = capacity
+
+    def _grow(self, B, H, D, needed, device):
+        cap = max(self._reserve, self.offset + needed)
+        cap = ((cap + self.step - 1) // self.step) * self.step
+        el = 32 // self.bits
+
+        def fresh():
+            return (torch.zeros((B, H, cap, D // el), dtype=torch.int32, device=device),
+                    torch.zeros((B, H, cap, D // self.group_size), dtype=torch.bfloat16, device=device),
+                    torch.zeros((B, H, cap, D // self.group_size), dtype=torch.bfloat16, device=device))
+        nk, nv = fresh(), fresh()
+        if self.keys is not None:
+            for new, old in zip(nk + nv, self.keys + self.values):
+                new[:, :, : self.offset] = old[:, :, : self.offset]
+        self.keys, self.values = nk, nv
+
+    def reserve(self, B, H, D, capacity, device="cuda"):
+        self._reserve = capacity
+        if self.keys is None or self.keys[0].shape[2] < capacity:
+            self._grow(B, H, D, 0, device)
+
+    def desc(self):
+        return ops.kvq_desc(self.keys, self.values, group_size=self.group_size, bits=self.bits)
+
+    def update_and_fetch(self, keys, values):
+        B, H, L, D = keys.shape
+        if self.keys is None or self.offset + L > self.keys[0].shape[2]:
+            self._grow(B, H, D, L, keys.device)
+        ops.kvq_write(self.desc(), keys, values, self.offset)
+        self.offset += L
+        return self.state
+
+    @property
+    def state(self):
+        if self.keys is None:
+            return None, None
+        cut = lambda t: t[:, :, : self.offset]
+        return tuple(map(cut, self.keys)), tuple(map(cut, self.values))
+
+    def trim(self, n: int) -> int:
+        n = min(self.offset, n)
+        self.offset -= n
+        return n
+
+    def is_trimmable(self) -> bool:
+        return True
+
+
+class PagedQuantizedKVCache:
+    """Quantised paged cache for one layer: pools [n_pages, n_kv, 64, D/4 | D/64] (head-major inside a page, so the 64
+    tokens of a (page, head) are one contiguous 8 KB run of quants) + an int32 page table [B, max_pages]."""
+    page_size = 64
+    group_size, bits = 64, 8
+
+    def __init__(self, n_pages: int, n_kv: int, D: int, page_table: torch.Tensor, device="cuda"):
+        def pool():
+            return (torch.zeros((n_pages, n_kv, self.page_size, D // 4), dtype=torch.int32, device=device),
+                    torch.zeros((n_pages, n_kv, self.page_size, D // 64), dtype=torch.bfloat16, device=device),
+                    torch.zeros((n_pages, n_kv, self.page_size, D // 64), dtype=torch.bfloat16, device=device))
+        self.keys, self.values = pool(), pool()
+        self.page_table = page_table
+        self.offset = 0
+
+    def desc(self):
+        return ops.kvq_desc(self.keys, self.values, self.page_table, self.page_size)
+
+    def update_and_fetch(self, keys, values):
+        L = keys.shape[2]
+        if self.offset + L > self.page_table.shape[1] * self.page_size:
+            raise ValueError("PagedQuantizedKVCache: page table too small for this many tokens")
+        ops.kvq_write(self.desc(), keys, values, self.offset)
+        self.offset += L
+        return self, self
+
+    def gather(self):
+        """Logical (quants, scales, biases) [B, n_kv, offset, .] copies of K and V (tests and the L > 1 attention)."""
+        t = torch.arange(self.offset, device=self.page_table.device)
+        pages = self.page_table[:, t // self.page_size].long()   # [B, T]
+        slot = (t % self.page_size)[None].expand(pages.shape[0], -1)
+        pick = lambda pool: pool[pages, :, slot].permute(0, 2, 1, 3).contiguous()   # [B, T, H, .] -> [B, H, T, .]
+        return tuple(map(pick, self.keys)), tuple(map(pick, self.values))

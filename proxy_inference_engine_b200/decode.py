@@ -24,7 +24,7 @@ import torch.distributed as dist
 
 from . import _lib, ops
 from ._lib import EPI_RESADD, EPI_SILUMUL, EPI_STORE, KvLayout, QmvSeg, StepIO, StepLayer, StepModel
-from .cache import KVCache, PagedKVCache
+from .cache import KVCache, PagedKVCache, PagedQuantizedKVCache, QuantizedKVCache
 from .llama import Model
 from .ops import _p, _stream
 
@@ -41,8 +41,10 @@ class DecodeEngine:
     def __init__(self, model: Model, batch: int = 1, max_context: int = 1024, paged: bool = False,
                  use_graph: bool = True, pdl: bool = True, keep_logits: bool = True, seed: int = 2,
                  fused: bool = False, trace: bool = False, attn_fused: bool | None = None, tp=None,
-                 sampling: dict | None = None):
-        """sampling: make_sampler's arguments (temp, top_p, min_p, min_tokens_to_keep, top_k; PIE/samplers/__init__.py:11)
+                 sampling: dict | None = None, kv_bits: int | None = None):
+        """kv_bits=8: the KV cache is the reference's QuantizedKVCache (8 bits, groups of 64; PIE/cache/kv_cache/quantized.py)
+        and the step's attention is pie_kvq_append + pie_decode_attn_q8.
+        sampling: make_sampler's arguments (temp, top_p, min_p, min_tokens_to_keep, top_k; PIE/samplers/__init__.py:11)
         plus `seed`; None or temp == 0 is greedy.  With temp > 0 every step ends in pie_sample instead of pie_argmax, inside
         the captured graph (the Philox draw counter lives in device memory), and token ids still never leave the GPU."""
         a = model.args
@@ -125,6 +127,19 @@ class DecodeEngine:
             rows = [self.page_allocator.allocate_pages(n_pg) for _ in range(B)]
             perm = torch.tensor(rows, dtype=torch.int32).to(dev)
             self.page_table = perm
+        self.kv_bits = kv_bits
+        if kv_bits is not None:
+            if fused or tp is not None:
+                raise ValueError("kv_bits: the quantised KV cache runs on the per-operator single-GPU path")
+            if paged:
+                self.cache = [PagedQuantizedKVCache(B * n_pg, self.Hkv, self.D, perm, dev) for _ in model.layers]
+            else:
+                self.cache = model.make_cache(max_context, kv_bits=kv_bits)
+                for c in self.cache:
+                    c.reserve(B, self.Hkv, self.D, max_context, dev)
+            self.kvq = [c.desc() for c in self.cache]   # host structs read at every launch: keep them alive
+            attn_fused = False
+        elif paged:
             self.cache = [PagedKVCache(torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev),
                                        torch.zeros((B * n_pg, 64, self.Hkv, self.D), dtype=bf, device=dev), perm)
                           for _ in model.layers]
@@ -140,7 +155,8 @@ class DecodeEngine:
             self.vbuf = [c.values for c in self.cache]
         L = _lib.load()
         self.L = L
-        self.nsplit = L.pie_decode_attn_pick_splits(B, self.Hq, self.Hkv, max_context)
+        self.nsplit = (L.pie_decode_attn_q8_pick_splits if kv_bits is not None else L.pie_decode_attn_pick_splits)(
+            B, self.Hq, self.Hkv, max_context)
         # Two forms of decode attention.  Latency form: rope + KV append + SIMT flash-decode in ONE launch
         # (pie_decode_attn_fused).  Throughput form: pie_rope_kv_append + the tensor-core kernel of pie_fa.cu, which
         # reads K/V once per kv head.  Measured per layer on B200 (tools/run_attn_compare.sh; 8B shapes, us):
@@ -282,11 +298,21 @@ class DecodeEngine:
                                                    self.Hkv, self.D,
                                                    float(ly.self_attn.scale), self.nsplit_fused, _p(self.attn_ws),
                                                    self.attn_ws.numel(), self.pdl, _stream()), "decode_attn_fused")
-            if "rope" not in skip and not self.attn_fused:
+            if self.kv_bits is not None:
+                if "rope" not in skip:
+                    _lib.check(L.pie_kvq_append(_p(self.q), _p(self.qkv), C.byref(self.kvq[i]), _p(self.positions),
+                                                _p(ly.self_attn.rope._freqs), self.B, self.Hq, self.Hkv, self.D,
+                                                _stream()), "kvq_append")
+                if "attn" not in skip:
+                    _lib.check(L.pie_decode_attn_q8(_p(self.attn), _p(self.q), C.byref(self.kvq[i]), _p(self.positions),
+                                                    self.B, self.Hq, self.Hkv, self.D, float(ly.self_attn.scale),
+                                                    self.nsplit, _p(self.attn_ws), self.attn_ws.numel(), _stream()),
+                               "decode_attn_q8")
+            elif "rope" not in skip and not self.attn_fused:
                 _lib.check(L.pie_rope_kv_append(_p(self.q), _p(self.qkv), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                             C.byref(self.lay[i]), _p(self.positions), _p(ly.self_attn.rope._freqs),
                                                 self.B, self.Hq, self.Hkv, self.D, _stream()), "rope_kv_append")
-            if "attn" not in skip and not self.attn_fused:
+            if "attn" not in skip and not self.attn_fused and self.kv_bits is None:
                 _lib.check(L.pie_decode_attn(_p(self.attn), _p(self.q), _p(self.kbuf[i]), _p(self.vbuf[i]),
                                          C.byref(self.lay[i]), _p(self.positions), self.B, self.Hq, self.Hkv, self.D,
                                          float(ly.self_attn.scale), self.nsplit, _p(self.attn_ws),
@@ -395,7 +421,7 @@ class DecodeEngine:
         Lp = ids.shape[1]
         if Lp + 1 > self.max_context:
             raise ValueError("prompt longer than the engine's max_context")
-        if self.paged:
+        if self.paged and self.kv_bits is None:
             tmp = self.model.make_cache(Lp)
             logits = self.model(ids, cache=tmp)
             for c, t in zip(self.cache, tmp):

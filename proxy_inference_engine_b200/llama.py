@@ -12,7 +12,7 @@ from dataclasses import dataclass, field
 import torch
 
 from . import nn, ops
-from .cache import KVCache, PagedKVCache
+from .cache import KVCache, PagedKVCache, PagedQuantizedKVCache, QuantizedKVCache
 from .tp import TPInfo, all_gather_last, all_reduce_sum
 
 
@@ -79,8 +79,27 @@ def create_attention_mask(h, cache=None):
     return None
 
 
+def quantized_scaled_dot_product_attention(queries, q_keys, q_values, scale, mask, group_size=64, bits=8, cache=None):
+    """base.py:56-89.  One query token: pie_decode_attn_q8 over the quantised cache in place (K, V and the scores are
+    never materialised).  L > 1 (prefill): the cached rows are expanded with mx.dequantize's arithmetic and go through
+    the causal prefill kernel -- the same contraction as the reference's two quantized_matmul calls."""
+    B, Hq, L, D = queries.shape
+    if L == 1 and mask is None and cache is not None:
+        Hkv = cache.keys[0].shape[1]
+        pos = torch.full((B,), cache.offset - 1, dtype=torch.int32, device=queries.device)
+        out = ops.decode_attention_q8(queries.reshape(B, Hq, D), cache.desc(), pos, scale, Hkv, max_context=cache.offset)
+        return out.view(B, Hq, 1, D)
+    if isinstance(q_keys, PagedQuantizedKVCache):
+        q_keys, q_values = q_keys.gather()
+    deq = lambda t: ops.dequantize(t[0].contiguous(), t[1].contiguous(), t[2].contiguous(), group_size=group_size, bits=bits)
+    return ops.scaled_dot_product_attention(queries, deq(q_keys), deq(q_values), scale=scale, mask=mask)
+
+
 def scaled_dot_product_attention(queries, keys, values, cache, scale, mask):
-    """base.py:92-113 (the non-quantized-KV branch)."""
+    """base.py:92-113."""
+    if isinstance(cache, (QuantizedKVCache, PagedQuantizedKVCache)):
+        return quantized_scaled_dot_product_attention(queries, keys, values, scale=scale, mask=mask,
+                                                      group_size=cache.group_size, bits=cache.bits, cache=cache)
     if isinstance(keys, PagedKVCache):
         c = keys
         B, Hq, L, D = queries.shape
@@ -228,7 +247,10 @@ class Model(nn.Module):
     def layers(self):
         return self.model.layers
 
-    def make_cache(self, capacity: int = 0):
+    def make_cache(self, capacity: int = 0, kv_bits: int | None = None, kv_group_size: int = 64):
+        """One cache per layer; kv_bits=8 gives the reference's QuantizedKVCache (PIE/cache/kv_cache/quantized.py)."""
+        if kv_bits is not None:
+            return [QuantizedKVCache(kv_group_size, kv_bits, capacity) for _ in self.layers]
         return [KVCache(capacity) for _ in self.layers]
 
     def parameters(self, prefix: str = "") -> dict:

@@ -12,7 +12,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import KvLayout, QmvSeg
+from ._lib import KvLayout, KvqCache, QmvSeg
 
 _BF16 = torch.bfloat16
 
@@ -291,6 +291,59 @@ def prefill_attention(q, kbuf, vbuf, lay: KvLayout, offset: int, scale: float):
     _lib.check(_lib.load().pie_prefill_attn(_p(out), _p(q.contiguous()), _p(kbuf), _p(vbuf), C.byref(lay), B, Hq, Hkv, Lq, D,
                                             int(offset), float(scale), _stream()), "scaled_dot_product_attention")
     return out.view(B, Lq, Hq, D).permute(0, 2, 1, 3)
+
+
+def kvq_desc(keys, values, page_table=None, page_size: int = 0, group_size: int = 64, bits: int = 8) -> KvqCache:
+    """pie_kvq_cache over the (quants, scales, biases) triples of a quantised KV cache: contiguous
+    [B, Hkv, cap, D/4 | D/64] (QuantizedKVCache's own arrays) or pools [pages, Hkv, page_size, .] + a page table."""
+    d = KvqCache()
+    for name, t in zip(("k_quant", "k_scales", "k_biases", "v_quant", "v_scales", "v_biases"), (*keys, *values)):
+        if not t.is_contiguous():
+            raise ValueError("quantised KV cache buffers must be contiguous")
+        setattr(d, name, t.data_ptr())
+    d.capacity = keys[0].shape[2]
+    if page_table is None:
+        d.page_table, d.pt_stride, d.page_size = None, 0, 0
+    else:
+        d.page_table, d.pt_stride, d.page_size = page_table.data_ptr(), page_table.stride(0), page_size
+    d.group_size, d.bits = group_size, bits
+    return d
+
+
+def kvq_append(qkv, desc: KvqCache, positions, freqs, Hq: int, Hkv: int, D: int, q_out=None):
+    """Decode step: rotate q and k of the fused projection output [B, (Hq + 2 Hkv) D] at positions[b], quantise k and v
+    into the cache (QuantizedKVCache.update_and_fetch, PIE/cache/kv_cache/quantized.py:92-106).  Returns q [B, Hq, D]."""
+    B = qkv.shape[0]
+    if q_out is None:
+        q_out = torch.empty((B, Hq, D), dtype=_BF16, device=qkv.device)
+    _lib.check(_lib.load().pie_kvq_append(_p(q_out), _p(qkv), C.byref(desc), _p(positions), _p(freqs), B, Hq, Hkv, D,
+                                          _stream()), "kvq_append")
+    return q_out
+
+
+def kvq_write(desc: KvqCache, keys, values, offset: int):
+    """Quantise k, v [B, Hkv, L, D] into cache rows offset .. offset + L - 1."""
+    B, Hkv, L, D = keys.shape
+    kc, vc = keys.contiguous(), values.contiguous()
+    _lib.check(_lib.load().pie_kvq_write(C.byref(desc), _p(kc), _p(vc), B, Hkv, L, D, offset, _stream()), "kvq_write")
+
+
+def decode_attention_q8(q, desc: KvqCache, positions, scale: float, Hkv: int, nsplit: int = 0, max_context: int = 0,
+                        out=None):
+    """quantized_scaled_dot_product_attention for one query token (PIE/models/base.py:56-89) over a quantised cache.
+    q [B, Hq, D]; positions int32 [B] (context = pos + 1) -> [B, Hq * D]."""
+    B, Hq, D = q.shape
+    L = _lib.load()
+    if nsplit <= 0:
+        nsplit = L.pie_decode_attn_q8_pick_splits(B, Hq, Hkv, max_context if max_context > 0 else 1)
+    nb = L.pie_decode_attn_workspace_bytes(B, Hq, D, nsplit)
+    ws = workspaces.get("attn", nb, q.device)
+    if out is None:
+        out = torch.empty((B, Hq * D), dtype=_BF16, device=q.device)
+    qc = q.contiguous()
+    _lib.check(L.pie_decode_attn_q8(_p(out), _p(qc), C.byref(desc), _p(positions), B, Hq, Hkv, D, float(scale), nsplit,
+                                    _p(ws), ws.numel(), _stream()), "decode_attn_q8")
+    return out
 
 
 def silu_mul(gate, up):

@@ -57,7 +57,7 @@ def make_oracle(args, weights, mode="B"):
 
 
 def run_decode_parity(args, prompt_len=16, steps=8, batch=1, seed=0, paged=False, use_graph=True, pdl=True,
-                      fused=False):
+                      fused=False, kv_bits=None):
     from proxy_inference_engine_b200.checkpoint import build_model, random_weights
     from proxy_inference_engine_b200.decode import DecodeEngine
 
@@ -66,9 +66,9 @@ def run_decode_parity(args, prompt_len=16, steps=8, batch=1, seed=0, paged=False
     o = make_oracle(args, w)
     prompt = torch.randint(0, args.vocab_size, (batch, prompt_len), generator=torch.Generator().manual_seed(1))
     eng = DecodeEngine(model, batch=batch, max_context=prompt_len + steps + 2, paged=paged, use_graph=use_graph,
-                       pdl=pdl, fused=fused)
+                       pdl=pdl, fused=fused, kv_bits=kv_bits)
     eng.prefill(prompt)
-    caches = o.make_cache()
+    caches = o.make_cache(kv_bits=kv_bits) if kv_bits is not None else o.make_cache()
     lo = o(prompt.numpy(), caches, last_only=True)[:, -1]
     errs, match, strong_mismatch, total = [], 0, 0, 0
     for _ in range(steps):
