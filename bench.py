@@ -374,7 +374,7 @@ def tp_subrecord(model_name, bits, batches, rank, world, prompt=128, steps=32):
     return {"workload": f"{model_name} random-init MLX q{bits} gs64, tp{world}, prompt {prompt}", **out}
 
 
-def config3_subrecord(model_name, steps=24, warmup=4, batch=32, prompt=2048):
+def config3_subrecord(model_name, steps=24, warmup=4, batch=32, prompt=2048, kv_bits=None):
     """BASELINE configs[2]: 8-bit weights, batch 32, paged KV cache, 2k context on one GPU -- the other end of the metric's
     "bs 1/32".  Random-init model of its own (the headline model is 4-bit), device-timed like the headline value."""
     import torch
@@ -384,7 +384,7 @@ def config3_subrecord(model_name, steps=24, warmup=4, batch=32, prompt=2048):
     model = build_model(margs, random_weights(margs, seed=0, device="cuda"))
     nums = model_numbers(margs, 8)
     peak, _ = measured_peaks()
-    eng = DecodeEngine(model, batch=batch, max_context=prompt + steps + warmup + 40, paged=True)
+    eng = DecodeEngine(model, batch=batch, max_context=prompt + steps + warmup + 40, paged=True, kv_bits=kv_bits)
     ids = torch.randint(0, margs.vocab_size, (batch, prompt), generator=torch.Generator().manual_seed(1))
     eng.prefill(ids)
     eng.step(warmup)
@@ -393,8 +393,12 @@ def config3_subrecord(model_name, steps=24, warmup=4, batch=32, prompt=2048):
     e0.record(); eng.step(steps); e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
-    step_bytes = nums["weight_bytes"] + batch * ((prompt + warmup + steps / 2) * nums["kv_bytes_per_ctx_token"])
-    out = {"workload": f"{model_name} random-init MLX q8 gs64, bs{batch} greedy decode, paged KV, prompt {prompt}",
+    kv_tok = nums["kv_bytes_per_ctx_token"]
+    if kv_bits == 8:   # quants + bf16 scale and bias per 64-group instead of bf16 values (PIE/cache/kv_cache/quantized.py)
+        kv_tok = kv_tok * (64 + 4) // 128
+    step_bytes = nums["weight_bytes"] + batch * ((prompt + warmup + steps / 2) * kv_tok)
+    kv_name = "paged KV" if kv_bits is None else f"paged {kv_bits}-bit gs64 KV (QuantizedKVCache)"
+    out = {"workload": f"{model_name} random-init MLX q8 gs64, bs{batch} greedy decode, {kv_name}, prompt {prompt}",
            "tok_s": round(batch / (ms * 1e-3), 1), "ms_per_step": round(ms, 3), "steps": steps, "warmup": warmup,
            "bytes_per_step": int(step_bytes), "hbm_frac": round(step_bytes / (ms * 1e-3) / 1e9 / peak, 4),
            "matmul_kernel": "qmi_kernel (tcgen05.mma kind::i8 over the packed 8-bit weights)"}
@@ -576,6 +580,7 @@ def run_b200(a):
         del eng
         torch.cuda.empty_cache()
         line["config3_q8_bs32_paged_ctx2k"] = config3_subrecord(a.model)
+        line["config3_q8_bs32_paged_ctx2k_kv8"] = config3_subrecord(a.model, kv_bits=8)
     if not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(margs, a.bits)
     print(json.dumps(line), flush=True)

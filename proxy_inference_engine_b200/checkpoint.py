@@ -171,7 +171,10 @@ def _empty_model(args: ModelArgs, device) -> Model:
         pnn.QuantizedLinear.__init__, pnn.QuantizedEmbedding.__init__ = orig_ql, orig_qe
 
 
-def save_checkpoint(path: str, args: ModelArgs, weights: dict) -> None:
+def save_checkpoint(path: str, args: ModelArgs, weights: dict, max_shard_bytes: int | None = None) -> None:
+    """config.json + MLX-layout safetensors.  max_shard_bytes: split into ``model-0000i-of-0000n.safetensors`` files of at
+    most that size plus ``model.safetensors.index.json`` (``metadata.total_size``, ``weight_map``: tensor name -> file),
+    the sharded form mlx_lm / Hugging Face write for large models and PIE's loader globs (PIE/models/utils.py:62-66)."""
     from safetensors.torch import save_file
 
     os.makedirs(path, exist_ok=True)
@@ -179,23 +182,61 @@ def save_checkpoint(path: str, args: ModelArgs, weights: dict) -> None:
     with open(os.path.join(path, "config.json"), "w") as f:
         json.dump(cfg, f, indent=1)
     out = {k: (v.view(torch.uint32) if v.dtype == torch.int32 else v).cpu().contiguous() for k, v in weights.items()}
-    save_file(out, os.path.join(path, "model.safetensors"), metadata={"format": "mlx"})
+    if max_shard_bytes is None:
+        save_file(out, os.path.join(path, "model.safetensors"), metadata={"format": "mlx"})
+        return
+    shards, cur, cur_bytes = [], {}, 0
+    for k in sorted(out):                       # a layer's weight / scales / biases stay together where they fit
+        nb = out[k].numel() * out[k].element_size()
+        if cur and cur_bytes + nb > max_shard_bytes:
+            shards.append(cur)
+            cur, cur_bytes = {}, 0
+        cur[k] = out[k]
+        cur_bytes += nb
+    shards.append(cur)
+    weight_map, total = {}, 0
+    for i, sh in enumerate(shards):
+        name = f"model-{i + 1:05d}-of-{len(shards):05d}.safetensors"
+        save_file(sh, os.path.join(path, name), metadata={"format": "mlx"})
+        for k, v in sh.items():
+            weight_map[k] = name
+            total += v.numel() * v.element_size()
+    with open(os.path.join(path, "model.safetensors.index.json"), "w") as f:
+        json.dump({"metadata": {"total_size": total}, "weight_map": weight_map}, f, indent=1)
+
+
+def read_weights(path: str) -> dict:
+    """Every ``model*.safetensors`` under ``path`` (PIE/models/utils.py:62-66).  When ``model.safetensors.index.json`` is
+    present it is the manifest: a shard it names that is missing, or a tensor it maps that its shard does not hold, is an
+    error here (the reference would fail later, at load_weights, with a missing-parameter message)."""
+    from safetensors.torch import load_file
+
+    files = sorted(glob.glob(os.path.join(path, "model*.safetensors")))
+    if not files:
+        raise FileNotFoundError(f"No safetensors found in {path}")
+    weights = {}
+    for wf in files:
+        weights.update(load_file(wf))
+    index = os.path.join(path, "model.safetensors.index.json")
+    if os.path.exists(index):
+        with open(index) as f:
+            wm = json.load(f)["weight_map"]
+        have = {os.path.basename(f) for f in files}
+        missing = sorted(set(wm.values()) - have)
+        if missing:
+            raise FileNotFoundError(f"checkpoint index names shards that are not in {path}: {missing}")
+        lost = sorted(k for k in wm if k not in weights)
+        if lost:
+            raise ValueError(f"checkpoint index maps tensors no shard holds: {lost[:4]}{' ...' if len(lost) > 4 else ''}")
+    return weights
 
 
 def load_model(path: str, device="cuda") -> Model:
     """PIE/models/utils.py:51-125 for the Llama family."""
-    from safetensors.torch import load_file
-
     with open(os.path.join(path, "config.json")) as f:
         config = json.load(f)
-    files = glob.glob(os.path.join(path, "model*.safetensors"))
-    if not files:
-        raise FileNotFoundError(f"No safetensors found in {path}")
     if config.get("model_type", "llama") != "llama":
         raise ValueError(f"Model type {config.get('model_type')} not supported.")
     if "quantization" not in config:
         raise ValueError("only MLX-quantized checkpoints (config['quantization']) are on this path")
-    weights = {}
-    for wf in files:
-        weights.update(load_file(wf))
-    return build_model(ModelArgs.from_dict(config), weights, device)
+    return build_model(ModelArgs.from_dict(config), read_weights(path), device)

@@ -142,11 +142,13 @@ def test_decode_engine_is_deterministic_and_free_running():
     assert a.shape == (1, 24) and torch.equal(a, b)
 
 
-def test_checkpoint_roundtrip(tmp_path):
+@pytest.mark.parametrize("shard_bytes", [None, 200000])
+def test_checkpoint_roundtrip(tmp_path, shard_bytes):
     from proxy_inference_engine_b200.checkpoint import build_model, load_model, random_weights, save_checkpoint
     args = tiny_args(bits=4, tie=True)
     w = random_weights(args, seed=0, device="cuda", gen_device="cpu")
-    save_checkpoint(str(tmp_path), args, w)
+    save_checkpoint(str(tmp_path), args, w, max_shard_bytes=shard_bytes)
+    assert (shard_bytes is None) != (tmp_path / "model.safetensors.index.json").exists()
     m1, m2 = build_model(args, w), load_model(str(tmp_path))
     p1, p2 = m1.parameters(), m2.parameters()
     assert p1.keys() == p2.keys() and "lm_head.weight" not in p2
