@@ -220,14 +220,30 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
   const int j0 = split * per, j1 = min(tiles, j0 + per);
   const uint32_t sK = smem_u32(smem), sV = sK + NS * TILE;
 
+  // a thread copies chunk `cc` of rows rr, rr + RSTEP, ...: when the 64 keys of a stage lie in one page (or the cache is
+  // contiguous) and all exist, one address computation serves the whole stage and the rest are constant offsets
+  constexpr int RSTEP = kFaThreads / CPR, NIT = kFaBKV / RSTEP;
+  const int cc = tid % CPR, rr = tid / CPR;
+  const bool one_page = !a.kv.page_table || a.kv.page_size % kFaBKV == 0;
+  const size_t row_step = (size_t)RSTEP * a.kv.tok_stride;
+  const uint32_t dst0 = fa_tile_off<D>(rr, cc);   // (rr + k RSTEP) & 7 == rr & 7: the swizzle term does not move
   auto issue = [&](int j) {  // always commits one group (empty past the end): the wait below counts groups
     const uint32_t dk = sK + ((j - j0) % NS) * TILE, dv = sV + ((j - j0) % NS) * TILE;
-    for (int i = tid; j < j1 && i < kFaBKV * CPR; i += kFaThreads) {
-      const int r = i / CPR, c = i % CPR;
-      const int t = min(j * kFaBKV + r, p);
-      const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
-      cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
-      cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+    if (j < j1 && one_page && j * kFaBKV + kFaBKV - 1 <= p) {
+      const size_t off = fa_kv_addr(a.kv, b, kvh, j * kFaBKV + rr) + cc * 8;
+#pragma unroll
+      for (int k = 0; k < NIT; ++k) {
+        cp_async16(dk + dst0 + k * (RSTEP * D * 2), a.kc + off + k * row_step);
+        cp_async16(dv + dst0 + k * (RSTEP * D * 2), a.vc + off + k * row_step);
+      }
+    } else {
+      for (int i = tid; j < j1 && i < kFaBKV * CPR; i += kFaThreads) {
+        const int r = i / CPR, c = i % CPR;
+        const int t = min(j * kFaBKV + r, p);
+        const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
+        cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
+        cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+      }
     }
     cp_async_commit();
   };

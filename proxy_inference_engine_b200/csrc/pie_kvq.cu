@@ -13,6 +13,9 @@
 // end).  Bytes become floats with one PRMT + one FADD (0x4B000000 | byte = 2^23 + byte); everything fp32, online softmax
 // whose running maximum only moves when a score exceeds it by 8 (log2 units): the result is the same sum, the
 // rescaling multiplies leave the inner loop.
+#include <cuda_fp16.h>
+#include <stdlib.h>
+
 #include "pie_internal.h"
 #include "pie_ptx.cuh"
 
@@ -387,6 +390,278 @@ __global__ void __launch_bounds__(128, 2) decode_attn_q8_kernel(const DecAttnQAr
   if (threadIdx.x == 0) a.ws_cnt[cidx] = 0;
 }
 
+// ---- the same attention on tensor cores (D = 128, up to 8 query heads per kv head) ---------------------------------
+// mma.sync.m16n8k16 f16: the M rows are the query heads of a kv head, a CTA of 4 warps shares 64-key stages (K quants
+// 8 KB + V quants 8 KB + 16 bytes of scales per key, cp.async, XOR-swizzled rows), warp w owns keys 16w .. 16w + 15.
+// The quants never become fp32: 0x6400 | byte IS the f16 number 1024 + byte, one PRMT per two elements, and the
+// 1024 * sum(q) (scores) / 1024 * sum(p') (values) excess is subtracted from the fp32 accumulators afterwards.  Per
+// 64-group: scores = sk * (acc - 1024 qsum) + bk * qsum; values: the A operand is p * sv (f16), the bias term one
+// scalar per group.  The k-slots of a thread ({2j, 2j+1, 2j+8, 2j+9}) are mapped to 4 consecutive features so a B
+// fragment of K comes from one 32-bit word; output column n of value tile t is feature 64 G + 8 n + t so a thread's
+// bytes of a V row are one 64-bit word.
+constexpr int kQtKeys = 64, kQtStages = 3, kQtThreads = 128, kQtStageBytes = 2 * kQtKeys * 128 + kQtKeys * 16;
+
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float f16lo(uint32_t v) { return __half2float(__ushort_as_half((unsigned short)(v & 0xffffu))); }
+__device__ __forceinline__ float f16hi(uint32_t v) { return __half2float(__ushort_as_half((unsigned short)(v >> 16))); }
+
+__global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __grid_constant__ DecAttnQArgs a) {
+  constexpr int D = 128, PW = D + 2, NS = kQtStages;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_last;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, j = lane & 3;
+  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int n_rep = a.Hq / a.c.Hkv, qh0 = kvh * n_rep;
+  const int p = a.pos[b], ctx = p + 1;
+  const int tiles = (ctx + kQtKeys - 1) / kQtKeys, per = (tiles + a.nsplit - 1) / a.nsplit;
+  const int j0 = split * per, j1 = min(tiles, j0 + per);
+  const uint32_t s0 = smem_u32(smem);
+
+  // a stage: thread copies K / V chunk (tid & 7) of rows (tid >> 3) + 16 k, and the 4-byte scale words of 2 keys
+  auto issue = [&](int jt) {   // always commits one group (empty past the end)
+    if (jt < j1) {
+      const uint32_t dst = s0 + ((jt - j0) % NS) * kQtStageBytes;
+      const int cc = tid & 7, rr = tid >> 3;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int r = rr + 16 * k;
+        const size_t slot = kvq_slot(a.c, b, kvh, min(jt * kQtKeys + r, p));
+        const uint32_t off = r * 128 + ((cc ^ (r & 7)) << 4);
+        cp_async16(dst + off, a.c.kq + slot * 32 + cc * 4);
+        cp_async16(dst + kQtKeys * 128 + off, a.c.vq + slot * 32 + cc * 4);
+      }
+      {
+        const int key = tid >> 1, arr0 = (tid & 1) * 2;
+        const size_t slot = kvq_slot(a.c, b, kvh, min(jt * kQtKeys + key, p));
+        const uint16_t* p0 = arr0 ? a.c.vs : a.c.ks;
+        const uint16_t* p1 = arr0 ? a.c.vb : a.c.kb;
+        cp_async4(dst + 2 * kQtKeys * 128 + key * 16 + arr0 * 4, p0 + slot * 2);
+        cp_async4(dst + 2 * kQtKeys * 128 + key * 16 + arr0 * 4 + 4, p1 + slot * 2);
+      }
+    }
+    cp_async_commit();
+  };
+  for (int s = 0; s < NS - 1; ++s) issue(j0 + s);
+
+  // Q as f16 A fragments: row g = head qh0 + g; k-slots {2j, 2j+1 | 2j+8, 2j+9} of step kc in group G hold features
+  // 64 G + 16 j + 4 kc + {0, 1 | 2, 3}
+  uint32_t qf[2][4][2];
+  float qs[2];   // sum of the head's q over each 64-group
+  {
+    const bool valid = g < n_rep;
+    const uint16_t* qrow = a.q + ((size_t)b * a.Hq + qh0 + (valid ? g : 0)) * D;
+#pragma unroll
+    for (int G = 0; G < 2; ++G) {
+      const uint4 lo = ldcg128(qrow + 64 * G + 16 * j), hi = ldcg128(qrow + 64 * G + 16 * j + 8);
+      const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+      float t = 0.f;
+#pragma unroll
+      for (int kc = 0; kc < 4; ++kc) {
+        const float x0 = valid ? bf16lo(w[2 * kc]) : 0.f, x1 = valid ? bf16hi(w[2 * kc]) : 0.f;
+        const float x2 = valid ? bf16lo(w[2 * kc + 1]) : 0.f, x3 = valid ? bf16hi(w[2 * kc + 1]) : 0.f;
+        qf[G][kc][0] = pack_f16(x0, x1);
+        qf[G][kc][1] = pack_f16(x2, x3);
+        t += (f16lo(qf[G][kc][0]) + f16hi(qf[G][kc][0])) + (f16lo(qf[G][kc][1]) + f16hi(qf[G][kc][1]));
+      }
+      t += __shfl_xor_sync(0xffffffffu, t, 1);
+      t += __shfl_xor_sync(0xffffffffu, t, 2);
+      qs[G] = t;
+    }
+  }
+  float o[2][8][4];
+#pragma unroll
+  for (int G = 0; G < 2; ++G)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { o[G][i][0] = o[G][i][1] = o[G][i][2] = o[G][i][3] = 0.f; }
+  float m = -INFINITY, l = 0.f, psum[2] = {0.f, 0.f}, bacc[2] = {0.f, 0.f};
+  const float sl2e = a.scale_log2e;
+
+  for (int jt = j0; jt < j1; ++jt) {
+    issue(jt + NS - 1);
+    cp_async_wait<NS - 1>();
+    __syncthreads();
+    const uint32_t tk = s0 + ((jt - j0) % NS) * kQtStageBytes, tv = tk + kQtKeys * 128, ts = tv + kQtKeys * 128;
+    // ---- scores of this warp's 16 keys: [2 key tiles of 8][2 groups]
+    float sacc[2][2][4];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int G = 0; G < 2; ++G) {
+        sacc[nt][G][0] = sacc[nt][G][1] = sacc[nt][G][2] = sacc[nt][G][3] = 0.f;
+        const int key = warp * 16 + nt * 8 + g;
+        const uint4 w4 = lds128(tk + key * 128 + (((4 * G + j) ^ (key & 7)) << 4));
+        const uint32_t w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+        for (int kc = 0; kc < 4; ++kc)
+          mma_f16_16816(sacc[nt][G], qf[G][kc][0], 0u, qf[G][kc][1], 0u, __byte_perm(w[kc], 0x64646464u, 0x4140),
+                        __byte_perm(w[kc], 0x64646464u, 0x4342));
+      }
+    // ---- this thread's 4 keys (head g): keys 16 w + 8 nt + 2 j + e
+    float sc[2][2], svv[2][2][2], bvv[2][2][2];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int key = warp * 16 + nt * 8 + 2 * j + e;
+        const uint4 z = lds128(ts + key * 16);   // {sk, bk, sv, bv} x {group 0 (low half), group 1 (high half)}
+        const float S0 = sacc[nt][0][e] - 1024.f * qs[0], S1 = sacc[nt][1][e] - 1024.f * qs[1];
+        float v = bf16lo(z.x) * S0 + bf16lo(z.y) * qs[0] + bf16hi(z.x) * S1 + bf16hi(z.y) * qs[1];
+        v *= sl2e;
+        if (jt * kQtKeys + key > p) v = -INFINITY;
+        sc[nt][e] = v;
+        mx = fmaxf(mx, v);
+        svv[nt][e][0] = bf16lo(z.z); svv[nt][e][1] = bf16hi(z.z);
+        bvv[nt][e][0] = bf16lo(z.w); bvv[nt][e][1] = bf16hi(z.w);
+      }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    if (mx > m + 8.f) {   // move the reference point of the running sums (rare after the first stage)
+      const float c = exp2f(m - mx);   // m == -inf: 0, and everything it multiplies is 0
+      l *= c; psum[0] *= c; psum[1] *= c; bacc[0] *= c; bacc[1] *= c;
+#pragma unroll
+      for (int G = 0; G < 2; ++G)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { o[G][i][0] *= c; o[G][i][1] *= c; }
+      m = mx;
+    }
+    uint32_t pa[2][2];   // [group][key tile] = A registers a0 / a2: p * sv as f16 pairs (keys 2j, 2j + 1)
+    {
+      float pr[2][2];
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          pr[nt][e] = sc[nt][e] == -INFINITY ? 0.f : exp2f(sc[nt][e] - m);
+          l += pr[nt][e];
+        }
+#pragma unroll
+      for (int G = 0; G < 2; ++G)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          pa[G][nt] = pack_f16(pr[nt][0] * svv[nt][0][G], pr[nt][1] * svv[nt][1][G]);
+          psum[G] += f16lo(pa[G][nt]) + f16hi(pa[G][nt]);
+          bacc[G] = fmaf(pr[nt][0], bvv[nt][0][G], fmaf(pr[nt][1], bvv[nt][1][G], bacc[G]));
+        }
+    }
+    // ---- values: rows 2j, 2j+1, 2j+8, 2j+9 of this warp's keys; features 64 G + 8 g .. + 7 of each
+#pragma unroll
+    for (int G = 0; G < 2; ++G) {
+      uint32_t vw[4][2];
+#pragma unroll
+      for (int r4 = 0; r4 < 4; ++r4) {
+        const int key = warp * 16 + 2 * j + (r4 & 1) + (r4 >> 1) * 8;
+        const uint32_t ad = tv + key * 128 + (((4 * G + (g >> 1)) ^ (key & 7)) << 4) + (g & 1) * 8;
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(vw[r4][0]), "=r"(vw[r4][1]) : "r"(ad));
+      }
+#pragma unroll
+      for (int t2 = 0; t2 < 4; ++t2) {   // value tiles 2 t2, 2 t2 + 1 = byte 2 t2 (+1) of the 8-byte run
+        const int wd = t2 >> 1;
+        const uint32_t sel = (t2 & 1) ? 0x7362u : 0x5140u;
+        const uint32_t xab = __byte_perm(vw[0][wd], vw[1][wd], sel), xcd = __byte_perm(vw[2][wd], vw[3][wd], sel);
+        mma_f16_16816(o[G][2 * t2], pa[G][0], 0u, pa[G][1], 0u, __byte_perm(xab, 0x64646464u, 0x4140),
+                      __byte_perm(xcd, 0x64646464u, 0x4140));
+        mma_f16_16816(o[G][2 * t2 + 1], pa[G][0], 0u, pa[G][1], 0u, __byte_perm(xab, 0x64646464u, 0x4342),
+                      __byte_perm(xcd, 0x64646464u, 0x4342));
+      }
+    }
+    __syncthreads();
+  }
+  cp_async_wait<0>();
+#pragma unroll
+  for (int sft = 1; sft <= 2; sft <<= 1) {
+    l += __shfl_xor_sync(0xffffffffu, l, sft);
+#pragma unroll
+    for (int G = 0; G < 2; ++G) {
+      psum[G] += __shfl_xor_sync(0xffffffffu, psum[G], sft);
+      bacc[G] += __shfl_xor_sync(0xffffffffu, bacc[G], sft);
+    }
+  }
+  // per-warp partials -> shared memory (the stages are free: the loop ended with a barrier)
+  float* rec = reinterpret_cast<float*>(smem);  // [4 warps][n_rep][PW]
+  if (g < n_rep) {
+    float* r0 = rec + ((size_t)warp * n_rep + g) * PW;
+#pragma unroll
+    for (int G = 0; G < 2; ++G) {
+      const float fix = bacc[G] - 1024.f * psum[G];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        r0[64 * G + 8 * (2 * j) + i] = o[G][i][0] + fix;
+        r0[64 * G + 8 * (2 * j + 1) + i] = o[G][i][1] + fix;
+      }
+    }
+    if (j == 0) { r0[D] = m; r0[D + 1] = l; }
+  }
+  __syncthreads();
+  const size_t rec0 = ((size_t)b * a.Hq + qh0) * a.nsplit;
+  for (int i = tid; i < n_rep * D; i += kQtThreads) {
+    const int r = i / D, d = i % D;
+    float mn = -INFINITY;
+    for (int w = 0; w < 4; ++w) mn = fmaxf(mn, rec[((size_t)w * n_rep + r) * PW + D]);
+    float lt = 0.f, at = 0.f;
+    for (int w = 0; w < 4; ++w) {
+      const float* rw = rec + ((size_t)w * n_rep + r) * PW;
+      const float cw = rw[D] == -INFINITY ? 0.f : exp2f(rw[D] - mn);
+      lt += rw[D + 1] * cw;
+      at += rw[d] * cw;
+    }
+    if (a.nsplit == 1) {
+      a.out[((size_t)b * a.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+    } else {
+      float* pr = a.ws_part + (rec0 + (size_t)r * a.nsplit + split) * PW;
+      pr[d] = at;
+      if (d == 0) { pr[D] = mn; pr[D + 1] = lt; }
+    }
+  }
+  if (a.nsplit == 1) return;
+  __threadfence();
+  __syncthreads();
+  const int cidx = b * a.c.Hkv + kvh;
+  if (tid == 0) s_last = (atomicAdd(&a.ws_cnt[cidx], 1u) == (unsigned)a.nsplit - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int i = tid; i < n_rep * D; i += kQtThreads) {
+    const int r = i / D, d = i % D;
+    const float* pr = a.ws_part + (rec0 + (size_t)r * a.nsplit) * PW;
+    float mn = -INFINITY;
+    for (int s = 0; s < a.nsplit; ++s) mn = fmaxf(mn, ldcg_f32(pr + (size_t)s * PW + D));
+    float lt = 0.f, at = 0.f;
+    for (int s = 0; s < a.nsplit; ++s) {
+      const float ms = ldcg_f32(pr + (size_t)s * PW + D);
+      const float cw = ms == -INFINITY ? 0.f : exp2f(ms - mn);
+      lt += ldcg_f32(pr + (size_t)s * PW + D + 1) * cw;
+      at += ldcg_f32(pr + (size_t)s * PW + d) * cw;
+    }
+    a.out[((size_t)b * a.Hq + qh0 + r) * D + d] = f2bf(at / lt);
+  }
+  if (tid == 0) a.ws_cnt[cidx] = 0;
+}
+
+static cudaError_t launch_decode_attn_q8_tc(const DecAttnQArgs& a, int B, cudaStream_t st) {
+  const size_t smem = (size_t)kQtStages * kQtStageBytes;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(decode_attn_q8_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = true;
+  }
+  count_launch();
+  decode_attn_q8_tc_kernel<<<dim3(a.nsplit, a.c.Hkv, B), kQtThreads, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
 template <int D>
 static cudaError_t launch_decode_attn_q8_d(const DecAttnQArgs& a0, int B, int n_rep, cudaStream_t st) {
   DecAttnQArgs a = a0;
@@ -483,6 +758,9 @@ int pie_decode_attn_q8(void* out, const void* q, const pie_kvq_cache* cache, con
   const size_t cnt_bytes = (((size_t)B * Hq * sizeof(unsigned)) + 255) & ~(size_t)255;
   a.ws_cnt = reinterpret_cast<unsigned int*>(workspace);
   a.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + cnt_bytes);
+  // tensor-core kernel for head_dim 128 with up to 8 query heads per kv head (PIE_KVQ_TC=0: the SIMT kernel)
+  static const bool tc = [] { const char* e = getenv("PIE_KVQ_TC"); return !(e && e[0] == '0'); }();
+  if (tc && D == 128 && Hq / Hkv <= 8) return status_of(launch_decode_attn_q8_tc(a, B, (cudaStream_t)stream));
   return status_of(D == 128 ? launch_decode_attn_q8_d<128>(a, B, Hq / Hkv, (cudaStream_t)stream)
                             : launch_decode_attn_q8_d<64>(a, B, Hq / Hkv, (cudaStream_t)stream));
 }

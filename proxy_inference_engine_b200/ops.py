@@ -236,7 +236,9 @@ def decode_attention(q, kbuf, vbuf, lay: KvLayout, positions, scale: float, nspl
     if nsplit <= 0:
         nsplit = L.pie_decode_attn_pick_splits(B, Hq, Hkv, max_context if max_context > 0 else 1)
     nb = L.pie_decode_attn_workspace_bytes(B, Hq, D, nsplit)
-    ws = workspaces.get("attn", nb, q.device)
+    # keyed by the size of the counter region: the counters must be zero at a launch, and a buffer that served another
+    # (rows, heads) geometry holds that call's partial sums where this call's counters lie
+    ws = workspaces.get(("attn", (B * Hq * 4 + 255) // 256), nb, q.device)
     out = torch.empty((B, Hq * D), dtype=_BF16, device=q.device)
     _lib.check(L.pie_decode_attn(_p(out), _p(q), _p(kbuf), _p(vbuf), C.byref(lay), _p(positions), B, Hq, Hkv, D,
                                  float(scale), nsplit, _p(ws), ws.numel(), _stream()), "scaled_dot_product_attention")
@@ -337,7 +339,9 @@ def decode_attention_q8(q, desc: KvqCache, positions, scale: float, Hkv: int, ns
     if nsplit <= 0:
         nsplit = L.pie_decode_attn_q8_pick_splits(B, Hq, Hkv, max_context if max_context > 0 else 1)
     nb = L.pie_decode_attn_workspace_bytes(B, Hq, D, nsplit)
-    ws = workspaces.get("attn", nb, q.device)
+    # keyed by the size of the counter region: the counters must be zero at a launch, and a buffer that served another
+    # (rows, heads) geometry holds that call's partial sums where this call's counters lie
+    ws = workspaces.get(("attn", (B * Hq * 4 + 255) // 256), nb, q.device)
     if out is None:
         out = torch.empty((B, Hq * D), dtype=_BF16, device=q.device)
     qc = q.contiguous()

@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--ksplit", type=int, default=0)
     ap.add_argument("--graph", type=int, default=0, help="time N launches captured in one CUDA graph (no CPU launch cost)")
     ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--copies", type=int, default=0, help="weight copies to rotate through (0: enough to defeat L2; 1: L2-warm)")
     a = ap.parse_args()
     L = _lib.load()
     dev = "cuda"
@@ -36,7 +37,7 @@ def main():
     for name in a.shapes.split(","):
         Ns, K, epi, norm = SHAPES[name]
         per_copy = sum(Ns) * K * (a.bits / 8 + 4 / 64)
-        copies = max(2, int(400e6 // per_copy) + 1)
+        copies = a.copies or max(2, int(400e6 // per_copy) + 1)
         sets = []
         for _ in range(copies):
             segs = (_lib.QmvSeg * len(Ns))()
