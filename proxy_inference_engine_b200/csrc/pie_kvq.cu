@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(128, 2) decode_attn_q8_kernel(const DecAttnQAr
 // scalar per group.  The k-slots of a thread ({2j, 2j+1, 2j+8, 2j+9}) are mapped to 4 consecutive features so a B
 // fragment of K comes from one 32-bit word; output column n of value tile t is feature 64 G + 8 n + t so a thread's
 // bytes of a V row are one 64-bit word.
-constexpr int kQtKeys = 64, kQtStages = 3, kQtThreads = 128, kQtStageBytes = 2 * kQtKeys * 128 + kQtKeys * 16;
+constexpr int kQtKeys = 64, kQtStages = 4, kQtAhead = 2, kQtThreads = 128, kQtStageBytes = 2 * kQtKeys * 128 + kQtKeys * 16;
 
 __device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                               uint32_t b0, uint32_t b1) {
@@ -428,31 +428,46 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
   const int j0 = split * per, j1 = min(tiles, j0 + per);
   const uint32_t s0 = smem_u32(smem);
 
-  // a stage: thread copies K / V chunk (tid & 7) of rows (tid >> 3) + 16 k, and the 4-byte scale words of 2 keys
+  // a stage: thread copies K / V chunk (tid & 7) of rows (tid >> 3) + 16 k, and two 4-byte scale words of one key.
+  // The 64 keys of a stage are 64 consecutive slots (one page, or a contiguous cache): one slot computation per stage.
+  const int cc = tid & 7, rr = tid >> 3, skey = tid >> 1;
+  const bool one_run = !a.c.page_table || (a.c.page_size % kQtKeys) == 0;
+  const uint32_t off_kv = rr * 128 + ((cc ^ (rr & 7)) << 4);   // (rr + 16 k) & 7 == rr & 7
+  const uint32_t off_sc = 2 * kQtKeys * 128 + skey * 16 + (tid & 1) * 8;
+  const uint16_t* sc_a = (tid & 1) ? a.c.vs : a.c.ks;
+  const uint16_t* sc_b = (tid & 1) ? a.c.vb : a.c.kb;
   auto issue = [&](int jt) {   // always commits one group (empty past the end)
     if (jt < j1) {
       const uint32_t dst = s0 + ((jt - j0) % NS) * kQtStageBytes;
-      const int cc = tid & 7, rr = tid >> 3;
+      const int t0 = jt * kQtKeys, rmax = p - t0;   // rows beyond the last key re-read it (masked later)
+      if (one_run) {
+        const size_t slot0 = kvq_slot(a.c, b, kvh, t0);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int r = rr + 16 * k;
-        const size_t slot = kvq_slot(a.c, b, kvh, min(jt * kQtKeys + r, p));
-        const uint32_t off = r * 128 + ((cc ^ (r & 7)) << 4);
-        cp_async16(dst + off, a.c.kq + slot * 32 + cc * 4);
-        cp_async16(dst + kQtKeys * 128 + off, a.c.vq + slot * 32 + cc * 4);
-      }
-      {
-        const int key = tid >> 1, arr0 = (tid & 1) * 2;
-        const size_t slot = kvq_slot(a.c, b, kvh, min(jt * kQtKeys + key, p));
-        const uint16_t* p0 = arr0 ? a.c.vs : a.c.ks;
-        const uint16_t* p1 = arr0 ? a.c.vb : a.c.kb;
-        cp_async4(dst + 2 * kQtKeys * 128 + key * 16 + arr0 * 4, p0 + slot * 2);
-        cp_async4(dst + 2 * kQtKeys * 128 + key * 16 + arr0 * 4 + 4, p1 + slot * 2);
+        for (int k = 0; k < 4; ++k) {
+          const size_t slot = slot0 + min(rr + 16 * k, rmax);
+          cp_async16(dst + off_kv + k * 2048, a.c.kq + slot * 32 + cc * 4);
+          cp_async16(dst + kQtKeys * 128 + off_kv + k * 2048, a.c.vq + slot * 32 + cc * 4);
+        }
+        const size_t slot = slot0 + min(skey, rmax);
+        cp_async4(dst + off_sc, sc_a + slot * 2);
+        cp_async4(dst + off_sc + 4, sc_b + slot * 2);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const size_t slot = kvq_slot(a.c, b, kvh, t0 + min(rr + 16 * k, rmax));
+          cp_async16(dst + off_kv + k * 2048, a.c.kq + slot * 32 + cc * 4);
+          cp_async16(dst + kQtKeys * 128 + off_kv + k * 2048, a.c.vq + slot * 32 + cc * 4);
+        }
+        const size_t slot = kvq_slot(a.c, b, kvh, t0 + min(skey, rmax));
+        cp_async4(dst + off_sc, sc_a + slot * 2);
+        cp_async4(dst + off_sc + 4, sc_b + slot * 2);
       }
     }
     cp_async_commit();
   };
-  for (int s = 0; s < NS - 1; ++s) issue(j0 + s);
+  // kQtAhead stages in flight, one more than that in the ring: the stage refilled at step jt was read at step jt - 2,
+  // and the barrier of step jt - 1 already orders every warp behind that -- one barrier per stage, not two
+  for (int s = 0; s < kQtAhead; ++s) issue(j0 + s);
 
   // Q as f16 A fragments: row g = head qh0 + g; k-slots {2j, 2j+1 | 2j+8, 2j+9} of step kc in group G hold features
   // 64 G + 16 j + 4 kc + {0, 1 | 2, 3}
@@ -488,8 +503,8 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
   const float sl2e = a.scale_log2e;
 
   for (int jt = j0; jt < j1; ++jt) {
-    issue(jt + NS - 1);
-    cp_async_wait<NS - 1>();
+    issue(jt + kQtAhead);
+    cp_async_wait<kQtAhead>();
     __syncthreads();
     const uint32_t tk = s0 + ((jt - j0) % NS) * kQtStageBytes, tv = tk + kQtKeys * 128, ts = tv + kQtKeys * 128;
     // ---- scores of this warp's 16 keys: [2 key tiles of 8][2 groups]
@@ -576,9 +591,9 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
                       __byte_perm(xcd, 0x64646464u, 0x4342));
       }
     }
-    __syncthreads();
   }
   cp_async_wait<0>();
+  __syncthreads();   // every warp is done with the stages: they become the merge records
 #pragma unroll
   for (int sft = 1; sft <= 2; sft <<= 1) {
     l += __shfl_xor_sync(0xffffffffu, l, sft);
@@ -588,7 +603,7 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
       bacc[G] += __shfl_xor_sync(0xffffffffu, bacc[G], sft);
     }
   }
-  // per-warp partials -> shared memory (the stages are free: the loop ended with a barrier)
+  // per-warp partials -> shared memory
   float* rec = reinterpret_cast<float*>(smem);  // [4 warps][n_rep][PW]
   if (g < n_rep) {
     float* r0 = rec + ((size_t)warp * n_rep + g) * PW;
