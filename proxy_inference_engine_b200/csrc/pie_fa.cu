@@ -299,22 +299,33 @@ __global__ void __launch_bounds__(kFaThreads) fa_decode_kernel(const __grid_cons
     }
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    const float c0 = mn0 == -INFINITY ? 1.f : exp2f(m0 - mn0), c1 = mn1 == -INFINITY ? 1.f : exp2f(m1 - mn1);
-    const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
+    // the reference point (m0, m1) of the running sums only moves when a score exceeds it by 8 (log2 units): same sums,
+    // and the 64 rescaling multiplies of the accumulators leave the steady-state loop (probabilities stay below 2^8)
+    if (mx0 > m0 + 8.f) {
+      const float c0 = exp2f(m0 - mx0);   // m0 == -inf: 0, and everything it multiplies is 0
+      l0 *= c0;
+#pragma unroll
+      for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; }
+      m0 = mx0;
+    }
+    if (mx1 > m1 + 8.f) {
+      const float c1 = exp2f(m1 - mx1);
+      l1 *= c1;
+#pragma unroll
+      for (int i = 0; i < DT; ++i) { o[i][2] *= c1; o[i][3] *= c1; }
+      m1 = mx1;
+    }
+    const float ms0 = m0 == -INFINITY ? 0.f : m0, ms1 = m1 == -INFINITY ? 0.f : m1;
     const float p00 = exp2f(s[0][0] - ms0), p01 = exp2f(s[0][1] - ms0), p02 = exp2f(s[0][2] - ms1), p03 = exp2f(s[0][3] - ms1);
     const float p10 = exp2f(s[1][0] - ms0), p11 = exp2f(s[1][1] - ms0), p12 = exp2f(s[1][2] - ms1), p13 = exp2f(s[1][3] - ms1);
-    l0 = l0 * c0 + (p00 + p01 + p10 + p11);
-    l1 = l1 * c1 + (p02 + p03 + p12 + p13);
-    m0 = mn0; m1 = mn1;
+    l0 += (p00 + p01 + p10 + p11);
+    l1 += (p02 + p03 + p12 + p13);
     // P as a bf16 pair (hi + lo): 16 significant bits, so this kernel agrees with the fp32-probability SIMT kernel to
     // ~1e-4 and greedy tokens do not depend on which of the two the engine picked; the extra 16 MMAs ride under the
     // K/V stream (the kernel is HBM-bound)
     const uint32_t a0 = pack_bf16(p00, p01), a1 = pack_bf16(p02, p03), a2 = pack_bf16(p10, p11), a3 = pack_bf16(p12, p13);
     const uint32_t e0 = pack_bf16(p00 - bf16lo(a0), p01 - bf16hi(a0)), e1 = pack_bf16(p02 - bf16lo(a1), p03 - bf16hi(a1));
     const uint32_t e2 = pack_bf16(p10 - bf16lo(a2), p11 - bf16hi(a2)), e3 = pack_bf16(p12 - bf16lo(a3), p13 - bf16hi(a3));
-#pragma unroll
-    for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
 #pragma unroll
     for (int dj = 0; dj < DT; dj += 2) {
       uint32_t b0, b1, b2, b3;
