@@ -13,6 +13,10 @@ namespace pie {
 static std::atomic<unsigned long long> g_launches{0};
 static thread_local char g_cuda_err[256] = "";
 void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+bool pdl_aux_enabled() {
+  static const bool on = [] { const char* e = getenv("PIE_PDL_AUX"); return !(e && e[0] == '0'); }();
+  return on;
+}
 
 static int cuda_status(cudaError_t e) {
   if (e == cudaSuccess) return PIE_OK;

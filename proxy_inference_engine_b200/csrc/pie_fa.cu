@@ -433,9 +433,8 @@ cudaError_t launch_decode_attn_tc(uint16_t* out, const uint16_t* q, const uint16
   }
   const dim3 grid(nsplit, Hkv, B);
   count_launch();
-  if (D == 128) fa_decode_kernel<128><<<grid, kFaThreads, smem, st>>>(a);
-  else fa_decode_kernel<64><<<grid, kFaThreads, smem, st>>>(a);
-  return cudaGetLastError();
+  return D == 128 ? launch_pdl(fa_decode_kernel<128>, grid, dim3(kFaThreads), smem, st, a)
+                  : launch_pdl(fa_decode_kernel<64>, grid, dim3(kFaThreads), smem, st, a);
 }
 
 cudaError_t launch_prefill_attn_tc(uint16_t* out, const uint16_t* q, const uint16_t* kc, const uint16_t* vc,

@@ -119,6 +119,26 @@ cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vo
 
 void count_launch(int n = 1);
 
+// Launch `kernel` as a programmatic dependent of the stream's previous kernel: it may be scheduled while that kernel is
+// still running and must execute griddepcontrol.wait (pdl_wait) before touching anything an earlier kernel wrote.  Every
+// kernel launched this way waits at its top, so completion stays transitive along the stream.  PIE_PDL_AUX=0: plain launch.
+bool pdl_aux_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_aux_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 struct QmvPlan { int warps, grid, ksplit, kslice, ks_w, ntiles, mt; };
 QmvPlan plan_qmv(int M, long long rows_total, int K, int bits, int dual, int ksplit_hint, int force_warps);
 size_t qmv_ws_bytes(const QmvPlan& p);

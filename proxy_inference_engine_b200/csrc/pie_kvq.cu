@@ -673,8 +673,7 @@ static cudaError_t launch_decode_attn_q8_tc(const DecAttnQArgs& a, int B, cudaSt
     configured = true;
   }
   count_launch();
-  decode_attn_q8_tc_kernel<<<dim3(a.nsplit, a.c.Hkv, B), kQtThreads, smem, st>>>(a);
-  return cudaGetLastError();
+  return launch_pdl(decode_attn_q8_tc_kernel, dim3(a.nsplit, a.c.Hkv, B), dim3(kQtThreads), smem, st, a);
 }
 
 template <int D>
@@ -723,9 +722,8 @@ int pie_kvq_append(void* q_out, const void* qkv, const pie_kvq_cache* cache, con
   KvqArgs c;
   if (int s = kvq_check(cache, Hkv, D, &c)) return s;
   count_launch();
-  kvq_append_kernel<<<dim3(Hq + 2 * Hkv, B), D / 2, 0, (cudaStream_t)stream>>>((uint16_t*)q_out, (const uint16_t*)qkv, c,
-                                                                              positions, freqs, Hq, D);
-  return status_of(cudaGetLastError());
+  return status_of(launch_pdl(kvq_append_kernel, dim3(Hq + 2 * Hkv, B), dim3(D / 2), 0, (cudaStream_t)stream,
+                              (uint16_t*)q_out, (const uint16_t*)qkv, c, positions, freqs, Hq, D));
 }
 
 int pie_kvq_write(const pie_kvq_cache* cache, const void* k, const void* v, int B, int Hkv, int L, int D, int offset,

@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(1024) qmi_prep_kernel(int8_t* xq, float* rscal
   __shared__ float red[64];
   const int m = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   pdl_launch_dependents();   // the matmul's set-up (barriers, TMEM, descriptors) overlaps this kernel; it waits before loading
+  pdl_wait();                // launched as a programmatic dependent itself: x is the previous kernel's output
   const int nchunks = K / 8;   // K is a multiple of 128
   uint4 xb[2], wb[2];
   float ss = 0.f;
@@ -187,6 +188,7 @@ __global__ void __launch_bounds__(kQiThreads, 1) qmi_kernel(const __grid_constan
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = tmem_slot;
   pdl_wait();   // the planes, row scales and group sums of qmi_prep_kernel are complete and visible
+  pdl_launch_dependents();   // the next kernel may be scheduled as SMs free up; it waits for this grid before it reads
   // slice `sl` of a tile covers stages [kb, ke)
   auto k_range = [&](int sl, int& kb, int& ke) {
     const int nb4 = a.nstages / kQiBatchStages;   // whole batches: K is a multiple of 512
@@ -518,8 +520,8 @@ cudaError_t launch_qmi(void* out, int out_ld, const void* x, int x_ld, int M, in
     if (e != cudaSuccess) return e;
   }
   count_launch();
-  qmi_prep_kernel<<<kQiMb, 1024, 0, st>>>(xq, rscale, gsum, (const uint16_t*)x, x_ld, (const uint16_t*)norm_w, eps, M, K);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_pdl(qmi_prep_kernel, dim3(kQiMb), dim3(1024), 0, st, xq, rscale, gsum, (const uint16_t*)x, x_ld,
+                             (const uint16_t*)norm_w, eps, M, K);
   if (e != cudaSuccess) return e;
   const int units = a.ntiles * a.ksplit;
   const int grid = units < num_sms() ? units : num_sms();

@@ -85,8 +85,8 @@ cudaError_t launch_rope_kv_append(uint16_t* q_out, const uint16_t* qkv, uint16_t
                                   int Hkv, int D, cudaStream_t st) {
   if (B == 0) return cudaSuccess;
   count_launch();
-  rope_kv_append_kernel<<<dim3(Hq + 2 * Hkv, B), D / 2, 0, st>>>(q_out, qkv, kc, vc, kv, pos, freqs, Hq, Hkv, D);
-  return cudaGetLastError();
+  return launch_pdl(rope_kv_append_kernel, dim3(Hq + 2 * Hkv, B), dim3(D / 2), 0, st, q_out, qkv, kc, vc, kv, pos, freqs, Hq,
+                    Hkv, D);
 }
 
 // prefill: k, v [B, Hkv, L, D] -> cache rows offset .. offset + L - 1
