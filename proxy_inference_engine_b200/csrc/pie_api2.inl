@@ -87,7 +87,10 @@ int pie_decode_attn_pick_splits(int B, int Hq, int Hkv, int max_context) {
     ctas = B * Hkv * rg;
     want = 148 * 4;
   }
-  int ns = (want + ctas - 1) / ctas;
+  // ONE wave of resident CTAs, never a wave and a fraction: measured on B200 (8B shapes, paged, us per layer at
+  // 1 / 2 / 3 / 4 splits): bs32 ctx2048 (256 CTAs per split) 45 / 59 / 62 / 66; bs16 ctx4096 (128) 70 / 50 / 65 / 57;
+  // bs8 ctx2048 (64), 2 / 4 / 5 / 8 splits: 27 / 23 / 29 / 24
+  int ns = want / ctas;
   const int cap = (max_context + 63) / 64;  // >= 64 tokens (one stage) per split
   if (ns > cap) ns = cap;
   if (ns > 32) ns = 32;  // kFaMaxSplits (pie_fa.cu)

@@ -423,13 +423,10 @@ cudaError_t launch_decode_attn_tc(uint16_t* out, const uint16_t* q, const uint16
   a.ws_cnt = reinterpret_cast<unsigned int*>(ws);
   a.ws_part = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + cnt_bytes);
   const size_t smem = (size_t)2 * kFaDecStages * kFaBKV * D * 2;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fa_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kFaDecStages * kFaBKV * 128 * 2);
+  {  // per launch, not once per process: the attribute is per device
+    cudaError_t e = D == 128 ? cudaFuncSetAttribute(fa_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                             : cudaFuncSetAttribute(fa_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(fa_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kFaDecStages * kFaBKV * 64 * 2);
-    if (e != cudaSuccess) return e;
-    configured = true;
   }
   const dim3 grid(nsplit, Hkv, B);
   count_launch();
@@ -444,11 +441,9 @@ cudaError_t launch_prefill_attn_tc(uint16_t* out, const uint16_t* q, const uint1
   a.out = out; a.q = q; a.kc = kc; a.vc = vc; a.kv = kv; a.Hq = Hq; a.Hkv = Hkv; a.L = L; a.offset = offset;
   a.scale_log2e = scale * 1.4426950408889634f;
   const size_t smem = (size_t)4 * kFaBKV * D * 2;  // K and V, double-buffered
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(fa_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * kFaBKV * 128 * 2);
+  if (D == 128) {  // per launch, not once per process: the attribute is per device (head_dim 64 fits the default 48 KB)
+    cudaError_t e = cudaFuncSetAttribute(fa_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   const dim3 grid((L + kFaBQ - 1) / kFaBQ, Hq, B);
   count_launch();

@@ -118,6 +118,15 @@ cudaError_t launch_argmax(int32_t* out, const uint16_t* logits, int rows, int vo
                           int32_t* seq_out, int seq_ld, cudaStream_t st);
 
 void count_launch(int n = 1);
+// Function attributes (the dynamic shared-memory opt-in) are per device: `mask` remembers the devices already served.
+inline bool first_use_on_device(unsigned long long& mask) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (mask & bit) return false;
+  mask |= bit;
+  return true;
+}
 
 // Launch `kernel` as a programmatic dependent of the stream's previous kernel: it may be scheduled while that kernel is
 // still running and must execute griddepcontrol.wait (pdl_wait) before touching anything an earlier kernel wrote.  Every

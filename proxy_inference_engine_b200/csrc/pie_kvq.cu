@@ -666,11 +666,9 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
 
 static cudaError_t launch_decode_attn_q8_tc(const DecAttnQArgs& a, int B, cudaStream_t st) {
   const size_t smem = (size_t)kQtStages * kQtStageBytes;
-  static bool configured = false;
-  if (!configured) {
+  {  // per launch, not once per process: the attribute is per device
     cudaError_t e = cudaFuncSetAttribute(decode_attn_q8_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   count_launch();
   return launch_pdl(decode_attn_q8_tc_kernel, dim3(a.nsplit, a.c.Hkv, B), dim3(kQtThreads), smem, st, a);
@@ -743,7 +741,7 @@ int pie_kvq_write(const pie_kvq_cache* cache, const void* k, const void* v, int 
 int pie_decode_attn_q8_pick_splits(int B, int Hq, int Hkv, int max_context) {
   if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return 1;
   const int n_rep = Hq / Hkv, R = n_rep % 4 == 0 ? 4 : (n_rep % 2 == 0 ? 2 : 1);
-  const long long units = (long long)B * Hkv * (n_rep / R);
+  const long long units = (long long)B * Hkv * (n_rep <= 8 ? 1 : n_rep / R);   // <= 8: the tensor-core kernel, one CTA per kv head
   // two CTAs of four warps fit an SM; one wave of them, and at least 512 tokens per split: a CTA's fixed cost (q load,
   // ring fill, merge through the workspace) is worth about 200 tokens (measured: bs32 ctx2048 79 / 93 / 99 us at 1 / 2 /
   // 4 splits; bs1 ctx8192 31 / 37 / 60 us at 16 / 32 / 64)

@@ -387,13 +387,12 @@ cudaError_t launch_qmd(const QmvArgs& g, const uint16_t* x, int x_ld, int bits, 
   a.ws_part = ws_part; a.ws_cnt = ws_cnt;
   { const char* e = getenv("PIE_QMD_DBG"); a.dbg = e ? atoi(e) : 0; }
   const int smem = bits == 4 ? QdGeom<4>::SMEM : QdGeom<8>::SMEM;
-  static bool configured[2] = {false, false};
+  static unsigned long long configured[2] = {0, 0};   // per device
   const int idx = bits == 4 ? 0 : 1;
-  if (!configured[idx]) {
+  if (first_use_on_device(configured[idx])) {
     cudaError_t e = bits == 4 ? cudaFuncSetAttribute(qmd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)
                               : cudaFuncSetAttribute(qmd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    configured[idx] = true;
   }
   const int units = a.ntiles * a.ksplit;
   const int grid = units < num_sms() ? units : num_sms();

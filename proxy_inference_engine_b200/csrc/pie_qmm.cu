@@ -212,13 +212,12 @@ cudaError_t launch_qmm_tc(uint16_t* y, const uint16_t* x, const uint32_t* wq, co
   QmmArgs a;
   a.y = y; a.x = x; a.wq = wq; a.scales = s; a.biases = b; a.M = M; a.N = N; a.K = K;
   const size_t smem = (size_t)kQmmSmem;
-  static bool configured[2] = {false, false};
+  static unsigned long long configured[2] = {0, 0};   // per device
   const int idx = bits == 4 ? 0 : 1;
-  if (!configured[idx]) {
+  if (first_use_on_device(configured[idx])) {
     cudaError_t e = bits == 4 ? cudaFuncSetAttribute(qmm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
                               : cudaFuncSetAttribute(qmm_tc_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured[idx] = true;
   }
   const dim3 grid((N + kQmmBN - 1) / kQmmBN, (M + kQmmBM - 1) / kQmmBM);
   count_launch();

@@ -20,12 +20,11 @@ int num_sms() {
 template <int BITS, int MT, bool ONECOL>
 static cudaError_t launch_qmv_t(const QmvArgs& a, int warps, int grid, bool pdl, cudaStream_t st) {
   const size_t smem = qmv_smem_bytes(a.M, a.kslice, BITS, warps, MT);
-  static bool configured = false;  // opt in to the full 227 KB of dynamic shared memory once
-  if (!configured) {
+  static unsigned long long configured = 0;  // opt in to the full 227 KB of dynamic shared memory, once per device
+  if (first_use_on_device(configured)) {
     cudaError_t e = cudaFuncSetAttribute(qmv_kernel<BITS, MT, ONECOL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kQmvMaxSmem);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid, 1, 1);
@@ -43,12 +42,11 @@ static cudaError_t launch_qmv_t(const QmvArgs& a, int warps, int grid, bool pdl,
 
 static cudaError_t launch_qmv_smemargs(const QmvArgs& a, int warps, int grid, bool pdl, cudaStream_t st) {
   const size_t smem = qmv_smem_bytes(a.M, a.kslice, 4, warps, 1) + (size_t)warps * 32 * kQmvProdWords * 4;
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;
+  if (first_use_on_device(configured)) {
     cudaError_t e = cudaFuncSetAttribute(qmv_kernel_smemargs<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kQmvMaxSmem - 1024);
     if (e != cudaSuccess) return e;
-    configured = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid, 1, 1);

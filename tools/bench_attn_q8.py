@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--ctx", type=int, default=2048)
     ap.add_argument("--splits", type=int, nargs="*", default=[0])
+    ap.add_argument("--bf16-splits", type=int, nargs="*", default=[0])
     ap.add_argument("--hq", type=int, default=32)
     ap.add_argument("--hkv", type=int, default=8)
     ap.add_argument("--dim", type=int, default=128)
@@ -63,9 +64,12 @@ def main():
         nq = ns or L.pie_decode_attn_q8_pick_splits(B, Hq, Hkv, T)
         us = timed(lambda i: ops.decode_attention_q8(q, sets_q[i][1], pos, D ** -0.5, Hkv, nsplit=nq, out=out))
         rec["rows"].append({"kernel": "q8", "nsplit": nq, "us": round(us, 2), "GBps": round(bytes_q / us / 1e3, 1)})
-    us = timed(lambda i: ops.decode_attention(q, sets_b[i][0].k_pool, sets_b[i][0].v_pool, sets_b[i][1], pos, D ** -0.5,
-                                              max_context=T))
-    rec["rows"].append({"kernel": "bf16 (tensor-core flash-decode)", "us": round(us, 2), "GBps": round(bytes_b / us / 1e3, 1)})
+    for ns in a.bf16_splits:
+        nb = ns or L.pie_decode_attn_pick_splits(B, Hq, Hkv, T)
+        us = timed(lambda i: ops.decode_attention(q, sets_b[i][0].k_pool, sets_b[i][0].v_pool, sets_b[i][1], pos, D ** -0.5,
+                                                  nsplit=nb, max_context=T))
+        rec["rows"].append({"kernel": "bf16 (tensor-core flash-decode)", "nsplit": nb, "us": round(us, 2),
+                            "GBps": round(bytes_b / us / 1e3, 1)})
     rec["kv_bytes"] = {"q8": bytes_q, "bf16": bytes_b}
     print(json.dumps(rec))
 
