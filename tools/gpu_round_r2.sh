@@ -23,6 +23,9 @@ PIE_QMV2=0 timeout 300 python tools/bench_qmv.py --M 1 --graph 40 --pdl 1 > $OUT
 timeout 300 python tools/bench_step_parts.py > $OUT/step_parts.json 2>&1
 ( timeout 400 python bench.py --bits 8 --batch 32 --prompt 2048 --paged --steps 32 --warmup 4 --no-cpu-baseline --no-kernel-timing --no-prefill ) > $OUT/config3_q8_bs32_paged.json 2> $OUT/config3.err
 timeout 300 python tools/bench_prefill.py > $OUT/config4.json 2>&1
+timeout 300 python tools/bench_attn_q8.py --splits 0 --bf16-splits 0 > $OUT/attn_bs32.json 2>&1
+timeout 300 python tools/bench_step_parts.py --bits 8 --batch 32 --ctx 2048 > $OUT/step_parts_bs32.json 2>&1
+timeout 300 python tools/bench_qmv.py --M 32 --bits 8 --graph 40 --pdl 1 --shapes qkv,o,gate_up,down > $OUT/qmi_m32.json 2>&1
 timeout 300 python tools/timeline_step.py --layers 32 > $OUT/timeline_8b_ctx300.json 2> $OUT/timeline.err
 timeout 600 $CMD > $OUT/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:pie:: -c 1500 \
