@@ -100,6 +100,16 @@ def test_pick_splits_fills_the_machine_and_respects_context():
     assert 1 < s <= 64
     assert L.pie_decode_attn_pick_splits(32, 32, 8, 2048) <= s
     assert L.pie_decode_attn_pick_splits(0, 32, 8, 2048) == 1
+    # one wave of resident CTAs (2 per SM on 148 SMs), never a wave and a fraction: measured optimum on B200
+    assert L.pie_decode_attn_pick_splits(32, 32, 8, 2048) == 1      # 256 CTAs per split
+    assert L.pie_decode_attn_pick_splits(16, 32, 8, 4096) == 2
+    assert L.pie_decode_attn_pick_splits(8, 32, 8, 2048) == 4
+    assert L.pie_decode_attn_pick_splits(64, 32, 8, 2048) == 1      # more than a wave already
+    # quantised-KV kernels: same rule, and at least 512 tokens per split
+    assert L.pie_decode_attn_q8_pick_splits(32, 32, 8, 2048) == 1
+    assert L.pie_decode_attn_q8_pick_splits(16, 32, 8, 4096) == 2
+    assert L.pie_decode_attn_q8_pick_splits(1, 32, 8, 8192) == 16
+    assert L.pie_decode_attn_q8_pick_splits(1, 32, 8, 100) == 1
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
