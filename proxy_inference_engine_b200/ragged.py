@@ -106,8 +106,9 @@ class BatchDetails:
 
 def ragged_step(model, batch: BatchDetails, pools, all_logits: bool = False) -> torch.Tensor:
     """One forward step of ``model`` over ``batch``.  pools: per layer (k_pool, v_pool) bf16 [n_pages, 64, n_kv, D] --
-    the pools the block table's page ids index.  Returns logits [num_sequences, vocab] of each sequence's last token
-    (all_logits: [total_tokens, vocab])."""
+    the pools the block table's page ids index -- or, for the 8-bit KV cache of cache.PagedQuantizedKVCache, per layer
+    ((k_quants, k_scales, k_biases), (v_quants, v_scales, v_biases)) [n_pages, n_kv, 64, .].
+    Returns logits [num_sequences, vocab] of each sequence's last token (all_logits: [total_tokens, vocab])."""
     batch.validate()
     L = _lib.load()
     a = model.args
@@ -123,10 +124,15 @@ def ragged_step(model, batch: BatchDetails, pools, all_logits: bool = False) -> 
         at = ly.self_attn
         x = ly.input_layernorm(h)
         qkv = torch.cat([at.q_proj(x), at.k_proj(x), at.v_proj(x)], dim=-1).view(T, (Hq + 2 * Hkv) * D)
-        lay = ops.kv_layout(kp, table, PAGE_TOKENS)
-        _lib.check(L.pie_rope_kv_append(_p(q), _p(qkv), _p(kp), _p(vp), C.byref(lay), _p(pos), _p(at.rope._freqs), T, Hq,
-                                        Hkv, D, _stream()), "rope_kv_append")
-        o = ops.decode_attention(q, kp, vp, lay, pos, at.scale, max_context=max_ctx)     # [T, Hq * D]
+        if isinstance(kp, (tuple, list)):   # quantised pools: (quants, scales, biases) [n_pages, n_kv, 64, .] per K and V
+            desc = ops.kvq_desc(tuple(kp), tuple(vp), table, PAGE_TOKENS)
+            ops.kvq_append(qkv, desc, pos, at.rope._freqs, Hq, Hkv, D, q_out=q)
+            o = ops.decode_attention_q8(q, desc, pos, at.scale, Hkv, max_context=max_ctx)
+        else:
+            lay = ops.kv_layout(kp, table, PAGE_TOKENS)
+            _lib.check(L.pie_rope_kv_append(_p(q), _p(qkv), _p(kp), _p(vp), C.byref(lay), _p(pos), _p(at.rope._freqs), T,
+                                            Hq, Hkv, D, _stream()), "rope_kv_append")
+            o = ops.decode_attention(q, kp, vp, lay, pos, at.scale, max_context=max_ctx)     # [T, Hq * D]
         h = ops.add(h, at.o_proj(o[None]))
         h = ops.add(h, ly.mlp(ly.post_attention_layernorm(h)))
     if not all_logits:

@@ -89,3 +89,26 @@ def test_decode_only_batch_with_unequal_contexts():
     ref_pools = mk()
     for i, sid in enumerate(seq):
         assert rel_l2(lg[i], _alone(model, ref_pools, pages[sid], seq[sid])[-1]) < TOL, sid
+
+
+def test_ragged_step_over_the_quantised_cache():
+    """f3 + f4 together: the mixed step over 8-bit pools equals each sequence run alone through Model.__call__ over a
+    PagedQuantizedKVCache of its own pages (same kernels for the decode rows, dequantise + prefill kernel for the
+    prompts) and the oracle running QuantizedKVCache."""
+    from proxy_inference_engine_b200.cache import PagedQuantizedKVCache
+    from proxy_inference_engine_b200.ragged import BatchDetails, ragged_step
+    args, w, model, mk, alloc = _setup(128)
+    hkv, d, n_pages = args.num_key_value_heads, args.head_dim, 24
+    dummy = torch.zeros((1, 1), dtype=torch.int32, device="cuda")
+    caches = [PagedQuantizedKVCache(n_pages, hkv, d, dummy) for _ in range(args.num_hidden_layers)]
+    pools = [(c.keys, c.values) for c in caches]
+    rng = np.random.default_rng(2)
+    seq = {3: rng.integers(0, args.vocab_size, 70).tolist(), 4: rng.integers(0, args.vocab_size, 40).tolist()}
+    pages = {sid: alloc.allocate_pages((len(t) + 63) // 64) for sid, t in seq.items()}
+    ragged_step(model, BatchDetails.build([(4, seq[4][:39], 0, pages[4])]), pools)
+    b = BatchDetails.build([(3, seq[3], 0, pages[3]), (4, seq[4][39:], 39, pages[4])])
+    lg = ragged_step(model, b, pools).float().cpu().numpy()
+    o = make_oracle(args, w)
+    for i, sid in enumerate((3, 4)):
+        lo = o(np.asarray([seq[sid]], np.int32), o.make_cache(kv_bits=8), last_only=True)[0, -1]
+        assert rel_l2(lg[i], lo) < TOL, sid
