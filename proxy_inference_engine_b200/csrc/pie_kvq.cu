@@ -397,8 +397,9 @@ __global__ void __launch_bounds__(128, 2) decode_attn_q8_kernel(const DecAttnQAr
 // 1024 * sum(q) (scores) / 1024 * sum(p') (values) excess is subtracted from the fp32 accumulators afterwards.  Per
 // 64-group: scores = sk * (acc - 1024 qsum) + bk * qsum; values: the A operand is p * sv (f16), the bias term one
 // scalar per group.  The k-slots of a thread ({2j, 2j+1, 2j+8, 2j+9}) are mapped to 4 consecutive features so a B
-// fragment of K comes from one 32-bit word; output column n of value tile t is feature 64 G + 8 n + t so a thread's
-// bytes of a V row are one 64-bit word.
+// fragment of K comes from one 32-bit word.  The value product is transposed (V as the A operand, features x keys; p * sv
+// as B, keys x heads -- the score accumulators ARE that B fragment): every accumulator row is live, and rows g, g + 8 of
+// value tile (G, q) are features 64 G + 8 g + 2 q + {0, 1}, so a thread's bytes of a V row are one 64-bit word.
 constexpr int kQtKeys = 64, kQtStages = 4, kQtAhead = 2, kQtThreads = 128, kQtStageBytes = 2 * kQtKeys * 128 + kQtKeys * 16;
 
 __device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
@@ -494,11 +495,11 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
       qs[G] = t;
     }
   }
-  float o[2][8][4];
+  // value accumulators, transposed: tile mt = 16 features (rows g, g + 8 -> features 64 G + 8 g + 2 (mt & 3) + {0, 1},
+  // G = mt / 4) x 8 heads (columns 2j, 2j + 1): every row of every tile is live
+  float o[8][4];
 #pragma unroll
-  for (int G = 0; G < 2; ++G)
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { o[G][i][0] = o[G][i][1] = o[G][i][2] = o[G][i][3] = 0.f; }
+  for (int i = 0; i < 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
   float m = -INFINITY, l = 0.f, psum[2] = {0.f, 0.f}, bacc[2] = {0.f, 0.f};
   const float sl2e = a.scale_log2e;
 
@@ -542,14 +543,15 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
       }
     mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
     mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-    if (mx > m + 8.f) {   // move the reference point of the running sums (rare after the first stage)
-      const float c = exp2f(m - mx);   // m == -inf: 0, and everything it multiplies is 0
+    const bool mv = mx > m + 8.f;
+    if (__any_sync(0xffffffffu, mv)) {   // move the reference point of the running sums (rare after the first stage)
+      const float c = mv ? exp2f(m - mx) : 1.f;   // m == -inf: 0, and everything it multiplies is 0
       l *= c; psum[0] *= c; psum[1] *= c; bacc[0] *= c; bacc[1] *= c;
+      if (mv) m = mx;
+      // the accumulators of this thread belong to heads 2j and 2j + 1 (lanes 8j and 8j + 4 hold their factors)
+      const float ca = __shfl_sync(0xffffffffu, c, 8 * j), cb = __shfl_sync(0xffffffffu, c, 8 * j + 4);
 #pragma unroll
-      for (int G = 0; G < 2; ++G)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { o[G][i][0] *= c; o[G][i][1] *= c; }
-      m = mx;
+      for (int i = 0; i < 8; ++i) { o[i][0] *= ca; o[i][1] *= cb; o[i][2] *= ca; o[i][3] *= cb; }
     }
     uint32_t pa[2][2];   // [group][key tile] = A registers a0 / a2: p * sv as f16 pairs (keys 2j, 2j + 1)
     {
@@ -570,7 +572,8 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
           bacc[G] = fmaf(pr[nt][0], bvv[nt][0][G], fmaf(pr[nt][1], bvv[nt][1][G], bacc[G]));
         }
     }
-    // ---- values: rows 2j, 2j+1, 2j+8, 2j+9 of this warp's keys; features 64 G + 8 g .. + 7 of each
+    // ---- values, V as the A operand (features x keys) and p * sv as B (keys x heads): a thread's A registers are the
+    // bytes of features 64 G + 8 g + {2q, 2q + 1} of its four keys 2j, 2j+1, 2j+8, 2j+9
 #pragma unroll
     for (int G = 0; G < 2; ++G) {
       uint32_t vw[4][2];
@@ -581,14 +584,12 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
         asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(vw[r4][0]), "=r"(vw[r4][1]) : "r"(ad));
       }
 #pragma unroll
-      for (int t2 = 0; t2 < 4; ++t2) {   // value tiles 2 t2, 2 t2 + 1 = byte 2 t2 (+1) of the 8-byte run
-        const int wd = t2 >> 1;
-        const uint32_t sel = (t2 & 1) ? 0x7362u : 0x5140u;
+      for (int q4 = 0; q4 < 4; ++q4) {   // bytes 2 q4, 2 q4 + 1 of the 8-byte run
+        const int wd = q4 >> 1;
+        const uint32_t sel = (q4 & 1) ? 0x7362u : 0x5140u;
         const uint32_t xab = __byte_perm(vw[0][wd], vw[1][wd], sel), xcd = __byte_perm(vw[2][wd], vw[3][wd], sel);
-        mma_f16_16816(o[G][2 * t2], pa[G][0], 0u, pa[G][1], 0u, __byte_perm(xab, 0x64646464u, 0x4140),
-                      __byte_perm(xcd, 0x64646464u, 0x4140));
-        mma_f16_16816(o[G][2 * t2 + 1], pa[G][0], 0u, pa[G][1], 0u, __byte_perm(xab, 0x64646464u, 0x4342),
-                      __byte_perm(xcd, 0x64646464u, 0x4342));
+        mma_f16_16816(o[4 * G + q4], __byte_perm(xab, 0x64646464u, 0x4140), __byte_perm(xab, 0x64646464u, 0x4342),
+                      __byte_perm(xcd, 0x64646464u, 0x4140), __byte_perm(xcd, 0x64646464u, 0x4342), pa[G][0], pa[G][1]);
       }
     }
   }
@@ -603,20 +604,30 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
       bacc[G] += __shfl_xor_sync(0xffffffffu, bacc[G], sft);
     }
   }
-  // per-warp partials -> shared memory
+  // per-warp partials -> shared memory; thread (g, j) holds heads 2j, 2j + 1 of features 64 G + 8 g + 2 q + {0, 1}
   float* rec = reinterpret_cast<float*>(smem);  // [4 warps][n_rep][PW]
-  if (g < n_rep) {
-    float* r0 = rec + ((size_t)warp * n_rep + g) * PW;
 #pragma unroll
-    for (int G = 0; G < 2; ++G) {
-      const float fix = bacc[G] - 1024.f * psum[G];
+  for (int G = 0; G < 2; ++G) {
+    const float fix = bacc[G] - 1024.f * psum[G];   // of head g: fetch those of heads 2j, 2j + 1
+    const float fa = __shfl_sync(0xffffffffu, fix, 8 * j), fb = __shfl_sync(0xffffffffu, fix, 8 * j + 4);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        r0[64 * G + 8 * (2 * j) + i] = o[G][i][0] + fix;
-        r0[64 * G + 8 * (2 * j + 1) + i] = o[G][i][1] + fix;
+    for (int q4 = 0; q4 < 4; ++q4) {
+      const int f = 64 * G + 8 * g + 2 * q4;
+      if (2 * j < n_rep) {
+        float* ra = rec + ((size_t)warp * n_rep + 2 * j) * PW;
+        ra[f] = o[4 * G + q4][0] + fa;
+        ra[f + 1] = o[4 * G + q4][2] + fa;
+      }
+      if (2 * j + 1 < n_rep) {
+        float* rb = rec + ((size_t)warp * n_rep + 2 * j + 1) * PW;
+        rb[f] = o[4 * G + q4][1] + fb;
+        rb[f + 1] = o[4 * G + q4][3] + fb;
       }
     }
-    if (j == 0) { r0[D] = m; r0[D + 1] = l; }
+  }
+  if (g < n_rep && j == 0) {
+    float* r0 = rec + ((size_t)warp * n_rep + g) * PW;
+    r0[D] = m; r0[D + 1] = l;
   }
   __syncthreads();
   const size_t rec0 = ((size_t)b * a.Hq + qh0) * a.nsplit;
@@ -665,7 +676,21 @@ __global__ void __launch_bounds__(kQtThreads) decode_attn_q8_tc_kernel(const __g
 }
 
 static cudaError_t launch_decode_attn_q8_tc(const DecAttnQArgs& a, int B, cudaStream_t st) {
-  const size_t smem = (size_t)kQtStages * kQtStageBytes;
+  size_t smem = (size_t)kQtStages * kQtStageBytes;
+  {
+    // Spread the grid: the block scheduler fills an SM to its residency limit before it moves on, so a grid of fewer
+    // CTAs than the machine can hold leaves SMs idle.  Asking for more shared memory than the kernel needs caps the
+    // residency at ceil(CTAs / SMs) and the grid covers every SM.
+    const long long ctas = (long long)a.nsplit * a.c.Hkv * B;
+    const int sms = num_sms();
+    long long per_sm = (ctas + sms - 1) / sms;
+    static const int force = [] { const char* e = getenv("PIE_KVQ_PER_SM"); return e ? atoi(e) : 0; }();
+    if (force > 0) per_sm = force;
+    if (per_sm >= 1 && per_sm <= 2) {
+      const size_t want = (size_t)(227 * 1024) / (size_t)per_sm - 1024 - 1152;   // 1 KB reserved per CTA + static
+      if (want > smem) smem = want & ~(size_t)127;
+    }
+  }
   {  // per launch, not once per process: the attribute is per device
     cudaError_t e = cudaFuncSetAttribute(decode_attn_q8_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
