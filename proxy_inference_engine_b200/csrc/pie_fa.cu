@@ -60,7 +60,9 @@ __global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_con
   constexpr int TILE = kFaBKV * D * 2;
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t4 = lane & 3;
-  const int q0 = blockIdx.x * kFaBQ, h = blockIdx.y, b = blockIdx.z;
+  // causal: query tile i needs i + 1 key tiles.  Blocks are dispatched in index order, so the LONGEST tiles go first
+  // (the last CTAs to start are then the one-tile ones and the grid's tail is short)
+  const int q0 = (int)(gridDim.x - 1 - blockIdx.x) * kFaBQ, h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (a.Hq / a.Hkv);
   const int T = a.offset + a.L;
   const uint32_t sK = smem_u32(smem), sV = sK + 2 * TILE;
