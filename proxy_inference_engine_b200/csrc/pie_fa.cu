@@ -71,14 +71,30 @@ __global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_con
   const int last_key = a.offset + min(q0 + kFaBQ, a.L) - 1;
   const int ntiles = last_key / kFaBKV + 1;
 
+  // a thread copies chunk `cc` of rows rr, rr + RSTEP, ...: when the 64 keys of a stage lie in one page (or the cache is
+  // contiguous) and all exist, one address computation serves the stage (as in fa_decode_kernel)
+  constexpr int RSTEP = kFaThreads / CPR, NIT = kFaBKV / RSTEP;
+  const int cc = tid % CPR, rr = tid / CPR;
+  const bool one_page = !a.kv.page_table || a.kv.page_size % kFaBKV == 0;
+  const size_t row_step = (size_t)RSTEP * a.kv.tok_stride;
+  const uint32_t dst0 = fa_tile_off<D>(rr, cc);   // (rr + k RSTEP) & 7 == rr & 7: the swizzle term does not move
   auto issue = [&](int j) {
     const uint32_t dk = sK + (j & 1) * TILE, dv = sV + (j & 1) * TILE;
-    for (int i = tid; i < kFaBKV * CPR; i += kFaThreads) {
-      const int r = i / CPR, c = i % CPR;
-      const int t = min(j * kFaBKV + r, T - 1);
-      const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
-      cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
-      cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+    if (one_page && j * kFaBKV + kFaBKV <= T) {
+      const size_t off = fa_kv_addr(a.kv, b, kvh, j * kFaBKV + rr) + cc * 8;
+#pragma unroll
+      for (int k = 0; k < NIT; ++k) {
+        cp_async16(dk + dst0 + k * (RSTEP * D * 2), a.kc + off + k * row_step);
+        cp_async16(dv + dst0 + k * (RSTEP * D * 2), a.vc + off + k * row_step);
+      }
+    } else {
+      for (int i = tid; i < kFaBKV * CPR; i += kFaThreads) {
+        const int r = i / CPR, c = i % CPR;
+        const int t = min(j * kFaBKV + r, T - 1);
+        const size_t off = fa_kv_addr(a.kv, b, kvh, t) + c * 8;
+        cp_async16(dk + fa_tile_off<D>(r, c), a.kc + off);
+        cp_async16(dv + fa_tile_off<D>(r, c), a.vc + off);
+      }
     }
     cp_async_commit();
   };
