@@ -158,9 +158,23 @@ __global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_con
     }
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
     mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-    const float c0 = mn0 == -INFINITY ? 1.f : exp2f(m0 - mn0), c1 = mn1 == -INFINITY ? 1.f : exp2f(m1 - mn1);
-    const float ms0 = mn0 == -INFINITY ? 0.f : mn0, ms1 = mn1 == -INFINITY ? 0.f : mn1;
+    // the reference point (m0, m1) of the running sums only moves when a score exceeds it by 8 (log2 units): same sums,
+    // and the rescaling multiplies of the accumulators leave the steady-state loop (probabilities stay below 2^8)
+    if (mx0 > m0 + 8.f) {
+      const float c0 = exp2f(m0 - mx0);   // m0 == -inf: 0, and everything it multiplies is 0
+      l0 *= c0;
+#pragma unroll
+      for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; }
+      m0 = mx0;
+    }
+    if (mx1 > m1 + 8.f) {
+      const float c1 = exp2f(m1 - mx1);
+      l1 *= c1;
+#pragma unroll
+      for (int i = 0; i < DT; ++i) { o[i][2] *= c1; o[i][3] *= c1; }
+      m1 = mx1;
+    }
+    const float ms0 = m0 == -INFINITY ? 0.f : m0, ms1 = m1 == -INFINITY ? 0.f : m1;
     float ps0 = 0.f, ps1 = 0.f;
     uint32_t pf[NT][2];
 #pragma unroll
@@ -171,10 +185,7 @@ __global__ void __launch_bounds__(kFaThreads) fa_prefill_kernel(const __grid_con
       pf[n][0] = pack_bf16(p0, p1);
       pf[n][1] = pack_bf16(p2, p3);
     }
-    l0 = l0 * c0 + ps0; l1 = l1 * c1 + ps1;
-    m0 = mn0; m1 = mn1;
-#pragma unroll
-    for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+    l0 += ps0; l1 += ps1;
     // ---- O += P V : contraction over the tile's 64 keys ------------------------------------------------------
 #pragma unroll
     for (int kk = 0; kk < kFaBKV / 16; ++kk) {
